@@ -1,0 +1,198 @@
+/*
+ * pfc_b200.h — C ABI of the B200-native per-timestep PFC hot path.
+ *
+ * The reference (lucasmyers97/phase-field-crystals) has no FFI: its hot path is three private
+ * methods of PhaseFieldCrystalSystemMPI<dim>
+ *   (src/phase_field_crystal_systems/phase_field_crystal_system_mpi.hpp:96-104, "mpi.hpp";
+ *    src/phase_field_crystal_systems/phase_field_crystal_system_mpi.cpp, "mpi.cpp").
+ * This header is the boundary a maintainer binds instead of those method bodies; every entry
+ * point names the reference lines it replaces.  Plain C types only; no exception crosses it.
+ *
+ * Ownership: the caller owns every host array; the library copies during the call and retains
+ * no host pointer.  All device memory belongs to the handle.
+ * Threading: one handle per GPU (per rank); a handle is not thread-safe.  With n_ranks > 1 the
+ * calls marked [collective] must be made by all ranks, like the MPI original.
+ * There is no CPU fallback: every compute entry point returns PFC_ERR_CUDA without a GPU.
+ */
+#ifndef PFC_B200_H
+#define PFC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* status codes (app/simulations/phase_field_crystal_simulation_mpi.cpp:172-180 catches C++
+ * exceptions and prints them; here every failure is a code + pfc_last_error text) */
+enum
+{
+  PFC_OK = 0,
+  PFC_ERR_BAD_ARGUMENT = 1,   /* std::invalid_argument in the reference */
+  PFC_ERR_CUDA = 2,           /* no device / CUDA runtime error */
+  PFC_ERR_NCCL = 3,
+  PFC_ERR_GMRES_NOT_CONVERGED = 4, /* deal.II SolverControl::NoConvergence at mpi.cpp:482 */
+  PFC_ERR_NONFINITE = 5,      /* NaN/Inf residual */
+  PFC_WARN_NEWTON_MAX_ITERS = 6, /* mpi.cpp:579-592: silently accepted by the reference */
+  PFC_ERR_UNSUPPORTED = 7,    /* input outside what the path handles (see pfc_setup) */
+  PFC_ERR_STATE = 8           /* call order (e.g. pfc_step before pfc_setup) */
+};
+
+enum { PFC_OPERATOR_ASSEMBLED = 0, PFC_OPERATOR_MATRIX_FREE = 1 };
+enum
+{
+  PFC_ORTHO_CGS = 0,   /* classical Gram-Schmidt, one fused pass, Kelley re-orthogonalisation test */
+  PFC_ORTHO_CGS2 = 1,  /* always two passes */
+  PFC_ORTHO_MGS = 2    /* modified Gram-Schmidt in the reference's operation order */
+};
+enum
+{
+  PFC_PRECOND_NONE = 0,        /* mpi.cpp:482 PreconditionIdentity (the reference's active path) */
+  PFC_PRECOND_BLOCK_SCHUR = 1  /* right preconditioner: lumped-mass block elimination + Chebyshev on
+                                  the psi Schur complement (cf. mpi.cpp:496-572, serial.cpp:319-369) */
+};
+
+/* Constructor arguments of the hot path: the subset of the 15-argument constructor
+ * (mpi.hpp:30-50) the per-timestep path reads, plus the deal.II defaults it relies on. */
+typedef struct pfc_params
+{
+  int32_t dim;                 /* 2 (dim 3 is instantiated upstream, mpi.cpp:716, but never run) */
+  int32_t degree;              /* FE_Q degree, 1 or 2 (mpi.cpp:84-86) */
+  double  dt, theta, eps;      /* mpi.hpp:80-84 */
+  double  newton_tol;          /* simulation_tol, absolute on ||-R||_2 (mpi.cpp:586) */
+  int32_t newton_max_iters;    /* simulation_max_iters (mpi.cpp:579) */
+  double  gmres_tol;           /* SolverControl default 1e-10 absolute (mpi.cpp:478) */
+  int64_t gmres_max_iters;     /* <= 0: n_dofs, as SolverControl(n_dofs) (mpi.cpp:478) */
+  int32_t gmres_n_tmp_vectors; /* <= 0: 30, deal.II default => restart length 28 */
+  int32_t operator_kind;       /* PFC_OPERATOR_* */
+  int32_t orthogonalization;   /* PFC_ORTHO_* */
+  int32_t preconditioner;      /* PFC_PRECOND_* */
+  int32_t precond_sweeps;      /* Chebyshev degree of the Schur solve (<= 0: default) */
+  int32_t device;              /* CUDA device ordinal; < 0: current device */
+  int32_t use_cuda_graph;      /* capture the GMRES restart cycle in a CUDA graph */
+} pfc_params;
+
+/* Flattened products of make_grid + setup_dofs (mpi.cpp:115-274) for the cells this rank
+ * integrates.  Single rank: all active cells.  Multi rank: owned cells first, then the one-cell
+ * ghost layer (mpi.cpp:178-186), so that every owned row is complete without compress(add)
+ * (mpi.cpp:464-466).  dof indices are global. */
+typedef struct pfc_mesh
+{
+  int64_t n_cells;            /* cells handed over (owned + ghost layer) */
+  int64_t n_owned_cells;      /* first n_owned_cells are locally owned (mpi.cpp:353) */
+  int64_t n_dofs;             /* global number of dofs (dof_handler.n_dofs(), mpi.cpp:478) */
+  int32_t dofs_per_cell;      /* fe_system.n_dofs_per_cell() (mpi.cpp:317): 12 or 27 */
+  int32_t n_q;                /* quadrature_formula.size() (mpi.cpp:318): 4 or 9 */
+  const double  *cell_vertices;      /* [n_cells][4][2] lexicographic; cells must be axis-aligned
+                                        rectangles (hyper_rectangle, mpi.cpp:119-122) */
+  const int32_t *cell_dofs;          /* [n_cells][dofs_per_cell], cell->get_dof_indices (mpi.cpp:453) */
+  const int32_t *local_component;    /* [dofs_per_cell] fe.system_to_component_index(i).first */
+  const int32_t *local_scalar_index; /* [dofs_per_cell] fe.system_to_component_index(i).second */
+  const double  *shape_value;        /* [n_q][n_s]    scalar FE_Q values at the Gauss points */
+  const double  *shape_grad_ref;     /* [n_q][n_s][2] reference-cell gradients */
+  const double  *q_weight;           /* [n_q] weights on the unit cell */
+  int64_t block_start[3];            /* first global dof of block psi, chi, phi (component_wise,
+                                        mpi.cpp:157-165); blocks must be index-congruent */
+  int64_t block_size[3];
+  /* AffineConstraints (mpi.cpp:188-217), closed; only identity periodic lines are supported:
+   * slave = 1.0 * master, inhomogeneity 0 */
+  int64_t        n_constraints;
+  const int32_t *constraint_slave;   /* [n_constraints] global dof */
+  const int32_t *constraint_master;  /* [n_constraints] global dof */
+  /* optional sparsity pattern of the host (mpi.cpp:232-244), monolithic CSR with ascending
+   * columns; if given, pfc_setup checks it is bit-identical to the pattern the library derives */
+  const int64_t *row_ptr;            /* [n_dofs + 1] or NULL */
+  const int32_t *col_idx;            /* [nnz] or NULL */
+  /* partition (single rank: n_ranks = 1, node_offsets may be NULL).  Rank r owns, in every
+   * block b, the contiguous dofs block_start[b] + [node_offsets[r], node_offsets[r+1])
+   * (owned_partitioning, mpi.cpp:167-176; all ranks' counts as from
+   * Utilities::MPI::all_gather of n_locally_owned_dofs_per_block). */
+  int32_t rank, n_ranks;
+  const int64_t *node_offsets;       /* [n_ranks + 1] */
+} pfc_mesh;
+
+/* per-call statistics of pfc_step: what the reference prints through pcout
+ * ("Residual is:" mpi.cpp:585, "Number of iterations:" mpi.cpp:483) and TimerOutput sections
+ * "assembly" / "solver" (mpi.cpp:303,474) */
+#define PFC_MAX_NEWTON_RECORD 256
+typedef struct pfc_step_stats
+{
+  int32_t status;              /* PFC_OK, PFC_WARN_NEWTON_MAX_ITERS, or an error */
+  int32_t n_assemblies;
+  int32_t n_solves;
+  int64_t gmres_iters_total;
+  double  residual[PFC_MAX_NEWTON_RECORD];     /* ||-R||_2 after each assembly */
+  int64_t gmres_iters[PFC_MAX_NEWTON_RECORD];  /* per solve */
+  double  gmres_final_residual[PFC_MAX_NEWTON_RECORD];
+  double  ms_assembly, ms_solver, ms_total;    /* CUDA-event times on the handle's stream */
+  int64_t kernel_launches;                     /* launches of this library's kernels */
+} pfc_step_stats;
+
+typedef struct pfc_handle pfc_handle;
+
+/* ---- lifecycle ------------------------------------------------------------------------- */
+void        pfc_default_params(pfc_params *p); /* values of parameter-files/hexagonal_lattice.toml */
+int         pfc_create(const pfc_params *p, pfc_handle **out);    /* ctor, mpi.cpp:50-111 */
+void        pfc_destroy(pfc_handle *h);
+const char *pfc_last_error(const pfc_handle *h);  /* h may be NULL: last error of pfc_create */
+const char *pfc_version(void);
+
+/* setup_dofs (mpi.cpp:150-274): derives the scalar pattern shared by the 7 coupled blocks,
+ * the periodic elimination, the colouring of the scatter; uploads; assembles the iterate-
+ * independent blocks once. */
+int pfc_setup(pfc_handle *h, const pfc_mesh *mesh);
+
+/* multi-GPU: a NCCL communicator per handle.  id_bytes is the 128-byte ncclUniqueId obtained
+ * by rank 0 from pfc_nccl_unique_id and broadcast by the host (MPI_COMM_WORLD at mpi.cpp:79). */
+int pfc_nccl_unique_id(void *id_bytes128);
+int pfc_comm_init(pfc_handle *h, const void *id_bytes128, int rank, int n_ranks);
+
+/* ---- state (mpi.cpp:278-296 writes Psi_n, Psi_n_1; output reads them mpi.cpp:597-619) ---- */
+int pfc_set_state(pfc_handle *h, const double *Psi_n, const double *Psi_n_1); /* [n_dofs] each */
+int pfc_get_state(pfc_handle *h, double *Psi_n, double *Psi_n_1);             /* either may be NULL */
+
+/* ---- the hot path ---------------------------------------------------------------------- */
+int pfc_assemble(pfc_handle *h);                        /* assemble_system, mpi.cpp:300-467 [collective] */
+int pfc_residual_norm(pfc_handle *h, double *norm);     /* system_rhs.l2_norm(), mpi.cpp:584 [collective] */
+int pfc_solve_update(pfc_handle *h, int64_t *gmres_iters, double *final_residual);
+                                                        /* solve_and_update_no_precondition, mpi.cpp:471-492 [collective] */
+int pfc_step(pfc_handle *h, pfc_step_stats *stats);     /* iterate_timestep, mpi.cpp:576-593 [collective] */
+int pfc_run(pfc_handle *h, int32_t n_timesteps, pfc_step_stats *last, double *ms_total);
+                                                        /* the loop of run(), mpi.cpp:685-688, without output */
+
+/* ---- inspection (parity tests; output_rhs mpi.cpp:623-645) ----------------------------- */
+int pfc_get_rhs(pfc_handle *h, double *rhs);            /* [n_dofs] */
+int64_t pfc_get_nnz(pfc_handle *h);
+int pfc_get_pattern(pfc_handle *h, int64_t *row_ptr, int32_t *col_idx);  /* monolithic CSR */
+int pfc_get_matrix_values(pfc_handle *h, double *values);               /* [nnz], same order */
+int pfc_apply_operator(pfc_handle *h, const double *x, double *y);      /* y = J x (assembled or matrix-free) */
+int pfc_get_dof_permutation(pfc_handle *h, int32_t *internal_of_node);  /* [N] internal row of scalar node */
+
+/* timing of one operator application on resident data (bench.py roofline leg): runs `reps`
+ * applications on the handle's stream between CUDA events, returns the mean in ms and the
+ * algorithmic bytes of one launch for the active layout */
+int pfc_time_operator(pfc_handle *h, int32_t reps, double *ms_mean, double *bytes_per_launch);
+int pfc_time_assembly(pfc_handle *h, int32_t reps, double *ms_mean, double *bytes_per_launch);
+
+/* ---- host stand-in for the deal.II products (deal.II is not available in this image) ----
+ * Produces exactly the arrays of pfc_mesh for the only mesh the reference builds: one
+ * hyper_rectangle coarse cell refined n_refines times, periodic in x and y (mpi.cpp:115-146),
+ * FESystem(FE_Q(degree)^3), component-wise numbering (mpi.cpp:155-158), periodic constraints
+ * (mpi.cpp:188-217).  `repetitions` > 1 extends the coarse mesh (not reachable upstream). */
+typedef struct pfc_standin pfc_standin;
+int  pfc_standin_create(int32_t degree, int32_t n_refines, double x0, double y0, double x1,
+                        double y1, int32_t rank, int32_t n_ranks, pfc_standin **out);
+void pfc_standin_destroy(pfc_standin *s);
+const pfc_mesh *pfc_standin_mesh(const pfc_standin *s);
+int64_t pfc_standin_n_nodes(const pfc_standin *s);             /* nodes per component */
+const double *pfc_standin_support_points(const pfc_standin *s); /* [N][2], node t <-> dof c*N+t */
+/* HexagonalLattice<dim>::value (src/phase_field_functions/hexagonal_lattice.cpp:52-77) interpolated
+ * at the support points, then constraints.distribute (mpi.cpp:285-288).  Psi: [n_dofs]. */
+int  pfc_standin_hexagonal_lattice(const pfc_standin *s, double A0, double psi0, int32_t n_dislocations,
+                                   const double *positions /*[n][2]*/, const double *burgers /*[n][2]*/,
+                                   double *Psi);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PFC_B200_H */

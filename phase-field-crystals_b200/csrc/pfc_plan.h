@@ -1,0 +1,80 @@
+// pfc_plan.h — host-side products of pfc_setup: everything the kernels index with.
+//
+// The reference builds these through deal.II in setup_dofs (mpi.cpp:150-274): DoF maps,
+// AffineConstraints, BlockSparsityPattern.  Here the flattened host arrays of pfc_mesh are
+// turned into the device layout described in DESIGN.md ("Data layout in HBM").
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/pfc_b200.h"
+
+namespace pfc
+{
+constexpr int kSlice = 32;      // SELL slice height = one warp
+constexpr int kSigma = 4096;    // sorting window (rows) of SELL-C-sigma
+
+struct Plan
+{
+  // sizes
+  int degree = 0, n_s = 0, n_q = 0, dpc = 0;
+  int64_t n_cells = 0;          // cells this rank integrates
+  int64_t N_global = 0;         // scalar nodes per component, global
+  int64_t n_dofs = 0;           // 3 N_global
+  int64_t block_start[3] = {0, 0, 0};
+  int rank = 0, n_ranks = 1;
+  std::vector<int64_t> node_offsets; // [n_ranks+1]
+  int64_t own0 = 0;             // first owned global node
+  int64_t n_owned = 0;          // owned scalar nodes
+  int64_t Np = 0;               // n_owned rounded up to kSlice: rows of the SELL matrix
+  int64_t n_ghost = 0;          // ghost scalar nodes
+  int64_t Lv = 0;               // vector length: 3*Np + 3*n_ghost (ghost tail interleaved [g][c])
+  // numbering.  internal id u: u < Np owned row, u >= Np ghost (Np + ghost index)
+  std::vector<int32_t> perm;        // [Np] internal row -> global node, -1 padding
+  std::vector<int32_t> iperm;       // [n_owned] (global node - own0) -> internal row
+  std::vector<int32_t> ghost_global;// [n_ghost] global node, sorted by (owner, id)
+  std::vector<int32_t> row_len;     // [Np] real entries of the row (0 padding)
+  std::vector<int32_t> row_master;  // [Np] internal id of the resolved master of the row's node
+                                    //      (== row if free, -1 padding); may be a ghost id
+  // SELL-32-sigma scalar pattern shared by the coupled blocks
+  int64_t n_slices = 0;
+  std::vector<int64_t> slice_ptr;   // [n_slices+1] offsets (in entries) into col/val arrays
+  std::vector<int32_t> col;         // [n_ent] internal column id; ~row on the single diagonal
+                                    //         entry of a constrained (slave) row; padding = row, 0.0
+  int64_t n_ent = 0;
+  // cells, sorted by colour
+  int n_colors = 0;
+  std::vector<int64_t> color_ptr;   // [n_colors+1]
+  std::vector<int32_t> cell_src;    // [n_cells] index of the cell in the caller's arrays
+  std::vector<int32_t> cell_gather; // [n_cells][n_s] internal id of the raw node (state gather)
+  std::vector<int32_t> cell_row;    // [n_cells][n_s] internal row of the resolved node, -1 if not owned
+  std::vector<int32_t> cell_pos;    // [n_cells][n_s][n_s] entry position of (m(a), m(b)), -1 if row not owned
+  std::vector<int32_t> cell_spos;   // [n_cells][n_s] entry position of the slave diagonal, -1 if not slave/owned
+  std::vector<double>  cell_h;      // [n_cells][2] hx, hy
+  // reference tables
+  std::vector<double> shape, dshape, qw;
+  // periodic slaves among local nodes: v[slave] = v[master]
+  std::vector<int32_t> slave_id, slave_master; // internal ids (slave is owned or ghost)
+  // halo (n_ranks > 1)
+  std::vector<int32_t> peers;           // ranks exchanged with
+  std::vector<int64_t> send_ptr;        // [n_peers+1] into send_rows
+  std::vector<int32_t> send_rows;       // internal owned rows to pack for each peer
+  std::vector<int64_t> recv_ptr;        // [n_peers+1] ghost index ranges (ghosts sorted by owner)
+  // monolithic view (single rank only): pattern the reference would build (mpi.cpp:232-244)
+  int64_t nnz_mono = 0;
+  std::string error;
+};
+
+// builds the plan; returns PFC_OK or an error code with plan.error set
+int build_plan(const pfc_mesh &mesh, int degree, Plan &plan);
+
+// monolithic CSR (mpi.cpp:220-244) derived from the plan (single rank): row_ptr [n_dofs+1],
+// col_idx [nnz], and for every monolithic entry where it lives: block id (0 B,1 C,2 D,3 K,4 M)
+// and the SELL entry position
+void monolithic_pattern(const Plan &plan, std::vector<int64_t> &row_ptr, std::vector<int32_t> &col_idx,
+                        std::vector<int8_t> *block_of, std::vector<int32_t> *pos_of);
+
+// requests the peers' send lists: needs_from[r] = global nodes this rank needs from rank r.
+// (the exchange of these lists happens in pfc_comm_init)
+} // namespace pfc
