@@ -192,6 +192,29 @@ int  pfc_standin_hexagonal_lattice(const pfc_standin *s, double A0, double psi0,
                                    const double *positions /*[n][2]*/, const double *burgers /*[n][2]*/,
                                    double *Psi);
 
+/* ---- host-only view of what pfc_setup derives (tests run it without a GPU) ------------------
+ * The same code path pfc_setup uses: shared scalar pattern in SELL-32-sigma order, internal
+ * permutation, colouring and scatter tables.  Pointers stay valid until pfc_plan_destroy. */
+typedef struct pfc_plan pfc_plan;
+typedef struct pfc_plan_view
+{
+  int32_t n_s, n_colors, rank, n_ranks;
+  int64_t n_cells, N_global, own0, n_owned, Np, n_ghost, Lv, n_slices, n_ent, nnz_mono, n_slaves, n_peers;
+  const int32_t *perm, *iperm, *ghost_global, *row_len, *row_master, *col;
+  const int64_t *slice_ptr, *color_ptr;
+  const int32_t *cell_src, *cell_gather, *cell_row, *cell_pos, *cell_spos;
+  const double  *cell_h;
+  const int32_t *slave_id, *slave_master;
+  const int32_t *peers;
+  const int64_t *recv_ptr;
+} pfc_plan_view;
+int  pfc_plan_build(const pfc_mesh *mesh, int32_t degree, pfc_plan **out, char *err, int32_t err_len);
+void pfc_plan_get_view(const pfc_plan *p, pfc_plan_view *view);
+/* monolithic CSR the reference would build (mpi.cpp:220-244) + where each entry lives:
+ * block_of 0 B, 1 C, 2 D, 3 K, 4 M; pos_of = entry position in the SELL arrays (single rank) */
+int  pfc_plan_monolithic(const pfc_plan *p, int64_t *row_ptr, int32_t *col_idx, int8_t *block_of, int32_t *pos_of);
+void pfc_plan_destroy(pfc_plan *p);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,17 @@
+// pfc_comm.h — multi-GPU plumbing: NCCL (loaded lazily with dlopen, so a single-GPU host needs
+// no NCCL at all) for the two exchanges the path has:
+//   halo of ghost entries before each operator application  (Epetra Import inside vmult, mpi.cpp:482)
+//   all-reduce of the Gram-Schmidt coefficients and norms    (MPI_Allreduce inside dots, mpi.cpp:482,584)
+#pragma once
+#include <cstddef>
+#include <cstdint>
+
+struct pfc_handle;
+
+namespace pfc
+{
+void comm_destroy(pfc_handle *h);
+int comm_exchange_send_lists(pfc_handle *h);           // after build_plan: fills plan.send_ptr / send_rows
+int halo_exchange(pfc_handle *h, double *v);           // v's ghost tail := owners' values (stream-ordered)
+int allreduce_sum(pfc_handle *h, double *dev, size_t n); // in place, stream-ordered; no-op on one rank
+} // namespace pfc

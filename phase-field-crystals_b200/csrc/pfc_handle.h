@@ -1,0 +1,107 @@
+// pfc_handle.h — the opaque handle behind the C ABI: device buffers, stream, NCCL communicator.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "pfc_krylov.cuh"
+#include "pfc_plan.h"
+
+struct ncclComm;
+
+namespace pfc
+{
+template <class T>
+struct DevBuf
+{
+  T *p = nullptr;
+  size_t n = 0;
+  cudaError_t alloc(size_t count)
+  {
+    release();
+    n = count;
+    if (count == 0)
+      return cudaSuccess;
+    return cudaMalloc((void **)&p, count * sizeof(T));
+  }
+  cudaError_t upload(const std::vector<T> &h, cudaStream_t s)
+  {
+    cudaError_t e = alloc(h.size());
+    if (e != cudaSuccess || h.empty())
+      return e;
+    return cudaMemcpyAsync(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, s);
+  }
+  void release()
+  {
+    if (p)
+      cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+  ~DevBuf() { release(); }
+  DevBuf() = default;
+  DevBuf(const DevBuf &) = delete;
+  DevBuf &operator=(const DevBuf &) = delete;
+};
+} // namespace pfc
+
+struct pfc_handle
+{
+  pfc_params prm;
+  std::string err;
+  int device = 0;
+  int n_sm = 148;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  bool is_setup = false, has_state = false, assembled = false;
+  pfc::Plan plan;
+  int64_t stride = 0; // doubles between Krylov basis vectors (Lv rounded up to 16)
+  int n_basis = 0;    // n_tmp_vectors - 1 basis vectors (v_0 .. v_restart)
+  int restart = 0;    // n_tmp_vectors - 2
+
+  // mesh tables
+  pfc::DevBuf<int32_t> d_cell_gather, d_cell_row, d_cell_pos, d_cell_spos, d_col, d_slave, d_slave_master;
+  pfc::DevBuf<double> d_cell_h, d_tab;
+  pfc::DevBuf<int64_t> d_slice_ptr, d_api_map;
+  // matrix blocks (SELL entry order) and vectors
+  pfc::DevBuf<double> d_B, d_C, d_M, d_K, d_rhs, d_psi_n, d_psi_n1, d_x, d_V, d_io;
+  // Krylov control
+  pfc::DevBuf<pfc::Ctl> d_ctl;
+  pfc::DevBuf<pfc::GmresSmall> d_small;
+  pfc::DevBuf<double> d_partial;
+  pfc::DevBuf<unsigned int> d_counter;
+  pfc::Ctl *h_ctl = nullptr; // pinned
+  double *h_scalar = nullptr; // pinned [4]
+  cudaGraphExec_t cycle_graph[2] = {nullptr, nullptr}; // [first cycle (x = 0), later cycles]
+
+  // multi-GPU
+  ncclComm *comm = nullptr;
+  int comm_rank = 0, comm_size = 1;
+  pfc::DevBuf<int32_t> d_send_rows;
+  pfc::DevBuf<double> d_send_buf;
+
+  int64_t launches = 0;
+
+  int fail(int code, const char *fmt, ...)
+  {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    err = buf;
+    return code;
+  }
+};
+
+#define PFC_CUDA(h, call)                                                                                      \
+  do                                                                                                           \
+    {                                                                                                          \
+      cudaError_t e_ = (call);                                                                                 \
+      if (e_ != cudaSuccess)                                                                                   \
+        return (h)->fail(PFC_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));     \
+    }                                                                                                          \
+  while (0)

@@ -1,0 +1,509 @@
+// pfc_solver.cu — drivers of the hot path: assemble_system (mpi.cpp:300-467), the GMRES solve
+// of solve_and_update_no_precondition (mpi.cpp:471-492) and the Newton loop of
+// iterate_timestep (mpi.cpp:576-593), all stream-ordered on the handle's stream.
+#include <cmath>
+#include <cstring>
+
+#include "pfc_comm.h"
+#include "pfc_handle.h"
+
+using namespace pfc;
+
+#define PFC_TRY(expr)            \
+  do                             \
+    {                            \
+      int rc_ = (expr);          \
+      if (rc_ != PFC_OK)         \
+        return rc_;              \
+    }                            \
+  while (0)
+
+static inline int vec_grid(const pfc_handle *h, int64_t n2)
+{
+  const int64_t need = (n2 + kVecThreads - 1) / kVecThreads;
+  const int64_t cap = (int64_t)h->n_sm * 4; // persistent grid-stride: 4 CTAs of 256 threads per SM
+  return (int)std::max<int64_t>(1, std::min<int64_t>(need, std::min<int64_t>(cap, 4096)));
+}
+
+// ---- assembly --------------------------------------------------------------------------------------
+template <int NS, bool CONST_PASS>
+static void launch_asm_colors(pfc_handle *h, const AsmArgs &A)
+{
+  const Plan &P = h->plan;
+  constexpr int cells_per_block = (32 / NS) * (kAsmThreads / 32);
+  for (int c = 0; c < P.n_colors; ++c)
+    {
+      const int64_t b = P.color_ptr[c], e = P.color_ptr[c + 1];
+      if (e <= b)
+        continue;
+      const int blocks = (int)((e - b + cells_per_block - 1) / cells_per_block);
+      assemble_kernel<NS, CONST_PASS><<<blocks, kAsmThreads, 0, h->stream>>>(A, b, e);
+      h->launches++;
+    }
+}
+
+int launch_assembly(pfc_handle *h, bool const_pass)
+{
+  const Plan &P = h->plan;
+  AsmArgs A;
+  A.cell_gather = h->d_cell_gather.p;
+  A.cell_row = h->d_cell_row.p;
+  A.cell_pos = h->d_cell_pos.p;
+  A.cell_spos = h->d_cell_spos.p;
+  A.cell_h = h->d_cell_h.p;
+  A.psi_n = h->d_psi_n.p;
+  A.psi_n1 = h->d_psi_n1.p;
+  A.B = h->d_B.p;
+  A.C = h->d_C.p;
+  A.M = h->d_M.p;
+  A.K = h->d_K.p;
+  A.rhs = h->d_rhs.p;
+  A.tab = h->d_tab.p;
+  A.Np = P.Np;
+  A.dt = h->prm.dt;
+  A.theta = h->prm.theta;
+  A.eps = h->prm.eps;
+  cudaStream_t s = h->stream;
+  if (const_pass)
+    {
+      PFC_CUDA(h, cudaMemsetAsync(h->d_M.p, 0, h->d_M.n * sizeof(double), s));
+      PFC_CUDA(h, cudaMemsetAsync(h->d_K.p, 0, h->d_K.n * sizeof(double), s));
+      if (P.n_s == 4)
+        launch_asm_colors<4, true>(h, A);
+      else
+        launch_asm_colors<9, true>(h, A);
+    }
+  else
+    {
+      // system_matrix = 0; system_rhs = 0 (mpi.cpp:305-306)
+      PFC_CUDA(h, cudaMemsetAsync(h->d_B.p, 0, h->d_B.n * sizeof(double), s));
+      PFC_CUDA(h, cudaMemsetAsync(h->d_C.p, 0, h->d_C.n * sizeof(double), s));
+      PFC_CUDA(h, cudaMemsetAsync(h->d_rhs.p, 0, h->d_rhs.n * sizeof(double), s));
+      if (P.n_s == 4)
+        launch_asm_colors<4, false>(h, A);
+      else
+        launch_asm_colors<9, false>(h, A);
+    }
+  PFC_CUDA(h, cudaGetLastError());
+  return PFC_OK;
+}
+
+// ---- operator application ----------------------------------------------------------------------------
+static int launch_spmv(pfc_handle *h, const double *x, double *y, const Ctl *ctl)
+{
+  const Plan &P = h->plan;
+  SpmvArgs S;
+  S.slice_ptr = h->d_slice_ptr.p;
+  S.col = h->d_col.p;
+  S.B = h->d_B.p;
+  S.C = h->d_C.p;
+  S.M = h->d_M.p;
+  S.K = h->d_K.p;
+  S.Np = P.Np;
+  S.n_slices = P.n_slices;
+  S.dtth = h->prm.dt * h->prm.theta;
+  const int blocks = (int)((P.n_slices * 32 + kSpmvThreads - 1) / kSpmvThreads);
+  spmv_sell_kernel<<<blocks, kSpmvThreads, 0, h->stream>>>(S, x, y, ctl);
+  h->launches++;
+  return PFC_OK;
+}
+
+// y = J x with the halo of x refreshed first (multi-rank)
+static int apply_operator(pfc_handle *h, double *x, double *y, const Ctl *ctl)
+{
+  PFC_TRY(halo_exchange(h, x));
+  return launch_spmv(h, x, y, ctl);
+}
+
+// ---- template dispatch over the Krylov dimension ---------------------------------------------------
+using DotFn = void (*)(const double *, int64_t, const double *, int64_t, double *, double *, unsigned int *, const Ctl *, int);
+using AxpyFn = void (*)(const double *, int64_t, double *, int64_t, const double *, double *, double *, unsigned int *, Ctl *, int);
+constexpr int kMaxDim = 32;
+template <int D>
+struct Tab
+{
+  static void fill(DotFn *d, AxpyFn *a)
+  {
+    d[D] = multidot_kernel<D>;
+    a[D] = multiaxpy_kernel<D>;
+    Tab<D - 1>::fill(d, a);
+  }
+};
+template <>
+struct Tab<0>
+{
+  static void fill(DotFn *d, AxpyFn *a)
+  {
+    d[0] = multidot_kernel<0>;
+    a[0] = nullptr;
+  }
+};
+static DotFn g_dot[kMaxDim + 1];
+static AxpyFn g_axpy[kMaxDim + 1];
+static bool g_tab_ready = false;
+static void ensure_tab()
+{
+  if (!g_tab_ready)
+    {
+      Tab<kMaxDim>::fill(g_dot, g_axpy);
+      g_tab_ready = true;
+    }
+}
+
+// ---- one restart cycle, enqueued on the stream (captured into a CUDA graph when enabled) -----------
+static int enqueue_cycle(pfc_handle *h, bool first_cycle)
+{
+  ensure_tab();
+  const Plan &P = h->plan;
+  cudaStream_t s = h->stream;
+  const int64_t n2 = 3 * P.Np / 2;
+  const int grid = vec_grid(h, n2);
+  Ctl *ctl = h->d_ctl.p;
+  GmresSmall *g = h->d_small.p;
+  double *V = h->d_V.p;
+  const int64_t st = h->stride;
+  double *partial = h->d_partial.p;
+  unsigned int *cnt = h->d_counter.p;
+  const int always = h->prm.orthogonalization == PFC_ORTHO_CGS2 ? 1 : 0;
+
+  // v0 = b - A x ; rho = ||v0|| ; check ; v0 /= rho          ([dealii-ext] start of the outer loop)
+  if (!first_cycle)
+    PFC_TRY(apply_operator(h, h->d_x.p, V, ctl));
+  residual_kernel<<<grid, kVecThreads, 0, s>>>(V, h->d_rhs.p, n2, first_cycle ? 0 : 1, partial, &g->nrm2[0], cnt, ctl);
+  h->launches++;
+  PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1));
+  cycle_begin_kernel<<<1, 1, 0, s>>>(g, ctl);
+  scale_kernel<<<grid, kVecThreads, 0, s>>>(V, n2, ctl);
+  h->launches += 2;
+
+  for (int inner = 0; inner < h->restart; ++inner)
+    {
+      const int dim = inner + 1;
+      double *w = V + (int64_t)dim * st;
+      PFC_TRY(apply_operator(h, V + (int64_t)inner * st, w, ctl)); // A.vmult
+      g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots0, cnt, ctl, 0);
+      PFC_TRY(allreduce_sum(h, g->dots0, dim + 1));
+      g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots0, partial, &g->nrm2[0], cnt, ctl, 0);
+      PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1));
+      ortho_decide_kernel<<<1, 1, 0, s>>>(g, ctl, dim, always);
+      g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots1, cnt, ctl, 1);
+      PFC_TRY(allreduce_sum(h, g->dots1, dim + 1));
+      g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots1, partial, &g->nrm2[1], cnt, ctl, 1);
+      PFC_TRY(allreduce_sum(h, &g->nrm2[1], 1));
+      givens_kernel<<<1, 1, 0, s>>>(g, ctl, inner);
+      scale_kernel<<<grid, kVecThreads, 0, s>>>(w, n2, ctl);
+      h->launches += 7;
+    }
+  backsolve_kernel<<<1, 1, 0, s>>>(g, ctl);
+  xupdate_kernel<<<grid, kVecThreads, 0, s>>>(V, st, h->d_x.p, n2, g, ctl);
+  h->launches += 2;
+  PFC_CUDA(h, cudaMemcpyAsync(h->h_ctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s));
+  PFC_CUDA(h, cudaGetLastError());
+  return PFC_OK;
+}
+
+static int run_cycle(pfc_handle *h, bool first_cycle)
+{
+  const int gi = first_cycle ? 0 : 1;
+  if (!h->prm.use_cuda_graph)
+    return enqueue_cycle(h, first_cycle);
+  if (!h->cycle_graph[gi])
+    {
+      const int64_t before = h->launches;
+      cudaGraph_t graph = nullptr;
+      PFC_CUDA(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+      const int rc = enqueue_cycle(h, first_cycle);
+      cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
+      if (rc != PFC_OK)
+        {
+          if (graph)
+            cudaGraphDestroy(graph);
+          return rc;
+        }
+      PFC_CUDA(h, e);
+      PFC_CUDA(h, cudaGraphInstantiate(&h->cycle_graph[gi], graph, 0));
+      cudaGraphDestroy(graph);
+      h->launches = before; // capture launched nothing
+    }
+  PFC_CUDA(h, cudaGraphLaunch(h->cycle_graph[gi], h->stream));
+  // kernels inside one cycle (see enqueue_cycle); halo packs excluded
+  h->launches += 3 + (first_cycle ? 0 : 1) + (int64_t)h->restart * 8 + 2;
+  return PFC_OK;
+}
+
+// GMRES as SolverGMRES::solve is used at mpi.cpp:478-482.  x := 0 (mpi.cpp:481).
+static int gmres_solve(pfc_handle *h, int64_t *iters, double *final_res)
+{
+  const Plan &P = h->plan;
+  cudaStream_t s = h->stream;
+  Ctl c0;
+  std::memset(&c0, 0, sizeof(c0));
+  c0.tol = h->prm.gmres_tol;
+  c0.max_iters = h->prm.gmres_max_iters > 0 ? h->prm.gmres_max_iters : P.n_dofs;
+  *h->h_ctl = c0;
+  PFC_CUDA(h, cudaMemcpyAsync(h->d_ctl.p, h->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, s));
+  PFC_CUDA(h, cudaMemsetAsync(h->d_x.p, 0, h->d_x.n * sizeof(double), s));
+  PFC_CUDA(h, cudaStreamSynchronize(s)); // h_ctl is reused as the read-back buffer
+  bool first = true;
+  for (;;)
+    {
+      PFC_TRY(run_cycle(h, first));
+      first = false;
+      PFC_CUDA(h, cudaStreamSynchronize(s));
+      if (h->h_ctl->state != 0)
+        break;
+    }
+  if (iters)
+    *iters = h->h_ctl->iters;
+  if (final_res)
+    *final_res = h->h_ctl->rho;
+  if (h->h_ctl->state == 2)
+    {
+      if (std::isnan(h->h_ctl->rho))
+        return h->fail(PFC_ERR_NONFINITE, "GMRES residual is NaN after %lld iterations", h->h_ctl->iters);
+      return h->fail(PFC_ERR_GMRES_NOT_CONVERGED, "GMRES did not converge in %lld iterations (residual %.3e)",
+                     h->h_ctl->iters, h->h_ctl->rho);
+    }
+  return PFC_OK;
+}
+
+// ---- C ABI: hot path ----------------------------------------------------------------------------------
+extern "C" int pfc_assemble(pfc_handle *h)
+{
+  if (!h)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->is_setup || !h->has_state)
+    return h->fail(PFC_ERR_STATE, "pfc_assemble needs pfc_setup and pfc_set_state first");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  PFC_TRY(launch_assembly(h, false));
+  h->assembled = true;
+  return PFC_OK;
+}
+
+static int residual_norm_async(pfc_handle *h)
+{
+  ensure_tab();
+  const int64_t n2 = 3 * h->plan.Np / 2;
+  GmresSmall *g = h->d_small.p;
+  g_dot[0]<<<vec_grid(h, n2), kVecThreads, 0, h->stream>>>(nullptr, 0, h->d_rhs.p, n2, h->d_partial.p, &g->nrm2[0],
+                                                            h->d_counter.p, nullptr, 0);
+  h->launches++;
+  PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1));
+  PFC_CUDA(h, cudaMemcpyAsync(h->h_scalar, &g->nrm2[0], sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  return PFC_OK;
+}
+
+extern "C" int pfc_residual_norm(pfc_handle *h, double *norm)
+{
+  if (!h || !norm)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->assembled)
+    return h->fail(PFC_ERR_STATE, "pfc_residual_norm before pfc_assemble");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  PFC_TRY(residual_norm_async(h));
+  PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+  *norm = std::sqrt(h->h_scalar[0]);
+  return PFC_OK;
+}
+
+extern "C" int pfc_solve_update(pfc_handle *h, int64_t *gmres_iters, double *final_residual)
+{
+  if (!h)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->assembled)
+    return h->fail(PFC_ERR_STATE, "pfc_solve_update before pfc_assemble");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  const Plan &P = h->plan;
+  PFC_TRY(gmres_solve(h, gmres_iters, final_residual));
+  // constraints.distribute(dPsi_n) (mpi.cpp:485); Psi_n += dPsi_n (mpi.cpp:487-491)
+  PFC_TRY(halo_exchange(h, h->d_x.p));
+  const int64_t nsl = (int64_t)P.slave_id.size();
+  if (nsl > 0)
+    {
+      distribute_kernel<<<(int)((nsl + 255) / 256), 256, 0, h->stream>>>(h->d_x.p, h->d_slave.p, h->d_slave_master.p, nsl, P.Np);
+      h->launches++;
+    }
+  axpy1_kernel<<<vec_grid(h, P.Lv), kVecThreads, 0, h->stream>>>(h->d_psi_n.p, h->d_x.p, P.Lv);
+  h->launches++;
+  PFC_CUDA(h, cudaGetLastError());
+  h->assembled = false;
+  return PFC_OK;
+}
+
+extern "C" int pfc_step(pfc_handle *h, pfc_step_stats *st)
+{
+  if (!h)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->is_setup || !h->has_state)
+    return h->fail(PFC_ERR_STATE, "pfc_step needs pfc_setup and pfc_set_state first");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  pfc_step_stats local;
+  if (!st)
+    st = &local;
+  std::memset(st, 0, sizeof(*st));
+  const int64_t launches0 = h->launches;
+  cudaStream_t s = h->stream;
+  PFC_CUDA(h, cudaEventRecord(h->ev[0], s));
+  int status = PFC_WARN_NEWTON_MAX_ITERS;
+  float ms;
+  for (int it = 0; it < h->prm.newton_max_iters; ++it) // mpi.cpp:579
+    {
+      PFC_CUDA(h, cudaEventRecord(h->ev[1], s));
+      PFC_TRY(launch_assembly(h, false)); // mpi.cpp:582
+      h->assembled = true;
+      PFC_TRY(residual_norm_async(h)); // mpi.cpp:584
+      PFC_CUDA(h, cudaEventRecord(h->ev[2], s));
+      PFC_CUDA(h, cudaStreamSynchronize(s));
+      PFC_CUDA(h, cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]));
+      st->ms_assembly += ms;
+      const double residual = std::sqrt(h->h_scalar[0]);
+      if (st->n_assemblies < PFC_MAX_NEWTON_RECORD)
+        st->residual[st->n_assemblies] = residual;
+      st->n_assemblies++;
+      if (!std::isfinite(residual))
+        {
+          st->status = PFC_ERR_NONFINITE;
+          return h->fail(PFC_ERR_NONFINITE, "non-finite Newton residual");
+        }
+      if (residual < h->prm.newton_tol) // mpi.cpp:586-587
+        {
+          status = PFC_OK;
+          break;
+        }
+      int64_t its = 0;
+      double fr = 0;
+      PFC_CUDA(h, cudaEventRecord(h->ev[1], s));
+      const int rc = pfc_solve_update(h, &its, &fr); // mpi.cpp:590
+      PFC_CUDA(h, cudaEventRecord(h->ev[2], s));
+      PFC_CUDA(h, cudaStreamSynchronize(s));
+      PFC_CUDA(h, cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]));
+      st->ms_solver += ms;
+      if (st->n_solves < PFC_MAX_NEWTON_RECORD)
+        {
+          st->gmres_iters[st->n_solves] = its;
+          st->gmres_final_residual[st->n_solves] = fr;
+        }
+      st->n_solves++;
+      st->gmres_iters_total += its;
+      if (rc != PFC_OK)
+        {
+          st->status = rc;
+          return rc;
+        }
+    }
+  // Psi_n_1 = Psi_n (mpi.cpp:592), also when Newton did not converge
+  PFC_CUDA(h, cudaMemcpyAsync(h->d_psi_n1.p, h->d_psi_n.p, h->d_psi_n.n * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  PFC_CUDA(h, cudaEventRecord(h->ev[3], s));
+  PFC_CUDA(h, cudaStreamSynchronize(s));
+  PFC_CUDA(h, cudaEventElapsedTime(&ms, h->ev[0], h->ev[3]));
+  st->ms_total = ms;
+  st->status = status;
+  st->kernel_launches = h->launches - launches0;
+  h->assembled = false;
+  return status == PFC_OK ? PFC_OK : PFC_WARN_NEWTON_MAX_ITERS;
+}
+
+extern "C" int pfc_run(pfc_handle *h, int32_t n_timesteps, pfc_step_stats *last, double *ms_total)
+{
+  if (!h || n_timesteps < 0)
+    return PFC_ERR_BAD_ARGUMENT;
+  double total = 0;
+  pfc_step_stats st;
+  int worst = PFC_OK;
+  for (int t = 0; t < n_timesteps; ++t) // mpi.cpp:685-688
+    {
+      const int rc = pfc_step(h, &st);
+      total += st.ms_total;
+      if (rc != PFC_OK && rc != PFC_WARN_NEWTON_MAX_ITERS)
+        {
+          if (last)
+            *last = st;
+          return rc;
+        }
+      if (rc != PFC_OK)
+        worst = rc;
+    }
+  if (last)
+    *last = st;
+  if (ms_total)
+    *ms_total = total;
+  return worst;
+}
+
+// ---- inspection / timing ---------------------------------------------------------------------------
+extern "C" int pfc_apply_operator(pfc_handle *h, const double *x, double *y)
+{
+  if (!h || !x || !y)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->assembled)
+    return h->fail(PFC_ERR_STATE, "pfc_apply_operator before pfc_assemble");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  const Plan &P = h->plan;
+  const int64_t n = P.n_dofs;
+  const int blocks = (int)((n + 255) / 256);
+  double *vx = h->d_V.p, *vy = h->d_V.p + h->stride;
+  PFC_CUDA(h, cudaMemsetAsync(vx, 0, h->stride * sizeof(double), h->stream));
+  PFC_CUDA(h, cudaMemcpyAsync(h->d_io.p, x, n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  scatter_kernel<<<blocks, 256, 0, h->stream>>>(vx, h->d_io.p, h->d_api_map.p, n);
+  h->launches++;
+  PFC_TRY(apply_operator(h, vx, vy, nullptr));
+  PFC_CUDA(h, cudaMemsetAsync(h->d_io.p, 0, n * sizeof(double), h->stream));
+  gather_kernel<<<blocks, 256, 0, h->stream>>>(h->d_io.p, vy, h->d_api_map.p, n, 3 * P.Np);
+  h->launches++;
+  PFC_CUDA(h, cudaGetLastError());
+  PFC_CUDA(h, cudaMemcpyAsync(y, h->d_io.p, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+  return PFC_OK;
+}
+
+extern "C" int pfc_time_operator(pfc_handle *h, int32_t reps, double *ms_mean, double *bytes_per_launch)
+{
+  if (!h || reps < 1 || !ms_mean)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->assembled)
+    return h->fail(PFC_ERR_STATE, "pfc_time_operator before pfc_assemble");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  const Plan &P = h->plan;
+  double *vx = h->d_V.p, *vy = h->d_V.p + h->stride;
+  for (int i = 0; i < 3; ++i)
+    PFC_TRY(launch_spmv(h, vx, vy, nullptr));
+  PFC_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
+  for (int i = 0; i < reps; ++i)
+    PFC_TRY(launch_spmv(h, vx, vy, nullptr));
+  PFC_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
+  PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+  float ms;
+  PFC_CUDA(h, cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]));
+  *ms_mean = ms / reps;
+  if (bytes_per_launch)
+    // layout-true algorithmic bytes: per stored entry col 4 + B,C,M,K 32; per row x read 24 + y write 24;
+    // slice pointers 8 per 32 rows
+    *bytes_per_launch = 36.0 * (double)P.n_ent + 48.0 * (double)P.Np + 8.0 * (double)P.n_slices;
+  return PFC_OK;
+}
+
+extern "C" int pfc_time_assembly(pfc_handle *h, int32_t reps, double *ms_mean, double *bytes_per_launch)
+{
+  if (!h || reps < 1 || !ms_mean)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->is_setup || !h->has_state)
+    return h->fail(PFC_ERR_STATE, "pfc_time_assembly needs pfc_setup and pfc_set_state first");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  const Plan &P = h->plan;
+  PFC_TRY(launch_assembly(h, false));
+  PFC_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
+  for (int i = 0; i < reps; ++i)
+    PFC_TRY(launch_assembly(h, false));
+  PFC_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
+  PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+  float ms;
+  PFC_CUDA(h, cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]));
+  *ms_mean = ms / reps;
+  h->assembled = true;
+  if (bytes_per_launch)
+    // B, C zeroed + written (read-modify-write counted once each way): 2 * 2 * 8 per entry;
+    // state read 48 / node, rhs write 24 / node; per cell tables (gather, row, spos, pos, h)
+    *bytes_per_launch = 32.0 * (double)P.n_ent + 72.0 * (double)P.Np +
+                        (double)P.n_cells * (4.0 * (3 * P.n_s + P.n_s * P.n_s) + 16.0);
+  return PFC_OK;
+}
