@@ -1,0 +1,165 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle — run with -m gpu on a B200.
+
+Tolerances (BASELINE.json north_star): psi relative L2 <= 1e-9 per step, <= 1e-7 after 100 steps;
+sparsity pattern and DoF maps bit-exact; assembled values <= 1e-13 relative to the row inf-norm.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+A = 4 * np.pi / np.sqrt(3.0)
+P1, P2 = (-6 * A, -5 * A), (6 * A, 5 * A)
+DISL, BURG = [[2 * A, 0], [-2 * A, 0]], [[A, 0], [-A, 0]]
+DT, EPS, PSI0 = 0.1, -0.8, -0.43
+
+
+def _setup(built, degree, n_refines, theta=1.0, dislocations=True, **kw):
+    import oracle as O
+    om = O.Mesh(degree, n_refines, P1, P2)
+    st = built.StandIn(degree, n_refines, P1, P2)
+    A0 = built.default_A0(PSI0, EPS)
+    Psi = st.hexagonal_lattice(A0, PSI0, DISL if dislocations else (), BURG if dislocations else ())
+    s = built.Solver(degree=degree, theta=theta, **kw)
+    s.setup(st)
+    return om, st, s, Psi
+
+
+def _rel(a, b):
+    return np.linalg.norm(a - b) / np.linalg.norm(b)
+
+
+@pytest.mark.parametrize("degree,n_refines,theta", [(1, 4, 1.0), (1, 6, 0.5), (2, 3, 1.0), (2, 5, 0.5), (1, 1, 1.0), (2, 1, 1.0)])
+def test_assembly_pattern_rhs_operator(built, degree, n_refines, theta):
+    om, st, s, Psi = _setup(built, degree, n_refines, theta)
+    N = om.N
+    Psi1 = Psi + 1e-2 * np.random.default_rng(7).standard_normal(Psi.size)
+    om.distribute(Psi1)
+    s.set_state(Psi1, Psi)
+    s.assemble()
+    rp, ci = s.get_pattern()
+    assert np.array_equal(rp, om.row_ptr) and np.array_equal(ci, om.col_idx)      # bit-exact
+    ovals, orhs = om.assemble(Psi1, Psi, DT, theta, EPS)
+    vals = s.get_matrix_values()
+    rown = np.maximum.reduceat(np.abs(ovals), om.row_ptr[:-1])
+    assert np.max(np.abs(vals - ovals) / np.repeat(rown, np.diff(om.row_ptr))) <= 1e-13
+    rhs = s.get_rhs()
+    assert np.max(np.abs(rhs - orhs)) <= 1e-13 * np.max(np.abs(orhs))
+    assert np.all(rhs[om.master >= 0] == 0.0)
+    assert abs(s.residual_norm() - np.linalg.norm(orhs)) <= 1e-13 * np.linalg.norm(orhs)
+    x = np.random.default_rng(3).standard_normal(3 * N)
+    y, ref = s.apply_operator(x), om.spmv(ovals, x)
+    assert np.max(np.abs(y - ref)) <= 1e-13 * np.max(np.abs(ref))
+    # state round trip through the internal permutation
+    a, b = s.get_state(want_n1=True)
+    assert np.array_equal(a, Psi1) and np.array_equal(b, Psi)
+    s.close()
+
+
+@pytest.mark.parametrize("degree,n_refines", [(1, 5), (2, 4)])
+def test_gmres_solve_matches_oracle(built, degree, n_refines):
+    om, st, s, Psi = _setup(built, degree, n_refines)
+    s.set_state(Psi, Psi)
+    s.assemble()
+    ovals, orhs = om.assemble(Psi, Psi, DT, 1.0, EPS)
+    its, res = s.solve_update()
+    xo, oits, conv, ores = om.gmres(ovals, orhs)
+    assert conv and res <= 1e-10
+    om.distribute(xo)
+    got = s.get_state() - Psi
+    # both solves stop at ||b - A x|| <= 1e-10 absolute: compare through the operator
+    assert np.linalg.norm(om.spmv(ovals, np.where(om.master >= 0, 0.0, got)) - orhs) <= 2e-10
+    assert _rel(got, xo) <= 1e-8
+    assert abs(its - oits) <= max(3, oits // 20), (its, oits)
+    s.close()
+
+
+@pytest.mark.parametrize("degree,n_refines,n_steps,kw", [
+    (1, 6, 3, {}),                                   # config 1: shipped TOML (hexagonal_lattice.toml)
+    (1, 6, 2, {"orthogonalization": 1}),             # CGS2
+    (1, 6, 2, {"use_cuda_graph": 0}),
+    (2, 4, 2, {}),
+    (1, 4, 2, {"theta": 0.5}),
+])
+def test_step_parity(built, degree, n_refines, n_steps, kw):
+    theta = kw.get("theta", 1.0)
+    om, st, s, Psi = _setup(built, degree, n_refines, **kw)
+    s.set_state(Psi, Psi)
+    Pn, Pn1 = Psi.copy(), Psi.copy()
+    N = om.N
+    for step in range(n_steps):
+        g = s.step()
+        o = om.newton_step(Pn, Pn1, DT, theta, EPS)
+        got = s.get_state()
+        assert g["status"] == 0 and o["status"] == 0
+        assert g["n_assemblies"] == o["n_assemblies"], (g["residuals"], o["residuals"])
+        err = _rel(got[:N], Pn[:N])
+        print(f"step {step}: gmres gpu {g['gmres_iters']} oracle {o['gmres_iters']} rel L2 psi {err:.2e}")
+        assert err <= 1e-9
+        assert _rel(got, Pn) <= 1e-9
+    s.close()
+
+
+def test_determinism_bitwise(built):
+    """no atomics: two runs give bit-identical matrices and states."""
+    outs = []
+    for _ in range(2):
+        om, st, s, Psi = _setup(built, 1, 5)
+        s.set_state(Psi, Psi)
+        s.assemble()
+        v = s.get_matrix_values()
+        s.step()
+        outs.append((v, s.get_state()))
+        s.close()
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+
+
+def test_mass_conservation_and_full_size_properties(built):
+    """Size-independent properties at a size the oracle would need minutes for (Q1, 2^9):
+    sum(M (psi_n - psi_{n-1})) == 0 (periodic conservation law), J linear, rows of K sum to 0."""
+    import oracle as O
+    degree, n_refines = 1, 9
+    st = built.StandIn(degree, n_refines, (-6 * A * 8, -5 * A * 8), (6 * A * 8, 5 * A * 8))
+    A0 = built.default_A0(PSI0, EPS)
+    Psi = st.hexagonal_lattice(A0, PSI0, [[16 * A, 0], [-16 * A, 0]], BURG)
+    s = built.Solver(degree=degree)
+    s.setup(st)
+    s.set_state(Psi, Psi)
+    g = s.step()
+    assert g["status"] == 0
+    new = s.get_state()
+    N = st.N
+    s.set_state(new, new)
+    s.assemble()
+    rng = np.random.default_rng(0)
+    x, y = rng.standard_normal(3 * N), rng.standard_normal(3 * N)
+    Jx, Jy, Jxy = s.apply_operator(x), s.apply_operator(y), s.apply_operator(2.0 * x - 3.0 * y)
+    assert np.max(np.abs(Jxy - (2 * Jx - 3 * Jy))) <= 1e-12 * np.max(np.abs(Jxy))
+    # chi-row: K x0 + M x1.  With x = (d, 0, 0), d = psi_new - psi_old: row block 1 gives K d;
+    # with x = (0, d, 0): row block 1 gives M d, whose sum over free rows is the mass change
+    d = np.zeros(3 * N)
+    d[N:2 * N] = new[:N] - Psi[:N]
+    free = np.ones(3 * N, bool)
+    free[st.constraint_slave] = False
+    d[~free] = 0.0
+    Md = s.apply_operator(d)[N:2 * N]
+    assert abs(Md[free[N:2 * N]].sum()) <= 1e-10 * np.abs(Md).sum()
+    one = np.zeros(3 * N)
+    one[:N] = 1.0
+    one[~free] = 0.0
+    K1 = s.apply_operator(one)[N:2 * N]
+    assert np.max(np.abs(K1[free[N:2 * N]])) <= 1e-12
+    s.close()
+
+
+def test_call_order_errors(built):
+    s = built.Solver()
+    for fn in (s.assemble, s.step, s.residual_norm, s.solve_update):
+        with pytest.raises(built.PfcError) as e:
+            fn()
+        assert e.value.code == built.PFC_ERR_STATE
+    with pytest.raises(built.PfcError):
+        built.Solver(degree=3)
+    with pytest.raises(built.PfcError):
+        built.Solver(dt=-1.0)
+    s.close()
