@@ -173,6 +173,10 @@ int pfc_get_dof_permutation(pfc_handle *h, int32_t *internal_of_node);  /* [N] i
  * algorithmic bytes of one launch for the active layout */
 int pfc_time_operator(pfc_handle *h, int32_t reps, double *ms_mean, double *bytes_per_launch);
 int pfc_time_assembly(pfc_handle *h, int32_t reps, double *ms_mean, double *bytes_per_launch);
+/* the two Gram-Schmidt kernels at Krylov dimension dim (1..restart): multi-dot (reads dim+1
+ * vectors) and multi-axpy with norm (reads dim+1, writes 1) */
+int pfc_time_krylov(pfc_handle *h, int32_t dim, int32_t reps, double *ms_dot, double *bytes_dot,
+                    double *ms_axpy, double *bytes_axpy);
 
 /* ---- host stand-in for the deal.II products (deal.II is not available in this image) ----
  * Produces exactly the arrays of pfc_mesh for the only mesh the reference builds: one
@@ -182,6 +186,10 @@ int pfc_time_assembly(pfc_handle *h, int32_t reps, double *ms_mean, double *byte
 typedef struct pfc_standin pfc_standin;
 int  pfc_standin_create(int32_t degree, int32_t n_refines, double x0, double y0, double x1,
                         double y1, int32_t rank, int32_t n_ranks, pfc_standin **out);
+/* rep_x x rep_y coarse cells instead of one (subdivided_hyper_rectangle; a harness extension
+ * for the weak-scaling meshes at 2 and 8 ranks): trees lexicographic, Morton inside */
+int  pfc_standin_create_ex(int32_t degree, int32_t n_refines, int32_t rep_x, int32_t rep_y, double x0,
+                           double y0, double x1, double y1, int32_t rank, int32_t n_ranks, pfc_standin **out);
 void pfc_standin_destroy(pfc_standin *s);
 const pfc_mesh *pfc_standin_mesh(const pfc_standin *s);
 int64_t pfc_standin_n_nodes(const pfc_standin *s);             /* nodes per component */

@@ -99,7 +99,8 @@ EXPORTED_SYMBOLS = [
     "pfc_nccl_unique_id", "pfc_comm_init", "pfc_set_state", "pfc_get_state", "pfc_assemble",
     "pfc_residual_norm", "pfc_solve_update", "pfc_step", "pfc_run", "pfc_get_rhs", "pfc_get_nnz",
     "pfc_get_pattern", "pfc_get_matrix_values", "pfc_apply_operator", "pfc_get_dof_permutation",
-    "pfc_time_operator", "pfc_time_assembly", "pfc_standin_create", "pfc_standin_destroy",
+    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_standin_create",
+    "pfc_standin_create_ex", "pfc_standin_destroy",
     "pfc_standin_mesh", "pfc_standin_n_nodes", "pfc_standin_support_points",
     "pfc_standin_hexagonal_lattice", "pfc_plan_build", "pfc_plan_get_view", "pfc_plan_monolithic",
     "pfc_plan_destroy",
@@ -168,6 +169,9 @@ def lib():
     L.pfc_time_assembly.argtypes = [hp, C.c_int32, _f64p, _f64p]
     L.pfc_standin_create.argtypes = [C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double,
                                      C.c_int32, C.c_int32, C.POINTER(hp)]
+    L.pfc_standin_create_ex.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_double,
+                                        C.c_double, C.c_double, C.c_int32, C.c_int32, C.POINTER(hp)]
+    L.pfc_time_krylov.argtypes = [hp, C.c_int32, C.c_int32, _f64p, _f64p, _f64p, _f64p]
     L.pfc_standin_destroy.argtypes = [hp]
     L.pfc_standin_destroy.restype = None
     L.pfc_standin_mesh.argtypes = [hp]
@@ -199,10 +203,10 @@ def default_A0(psi0: float, eps: float) -> float:
 class StandIn:
     """Host stand-in for make_grid + setup_dofs (mpi.cpp:115-274); see csrc/pfc_standin.cpp."""
 
-    def __init__(self, degree, n_refines, p1, p2, rank=0, n_ranks=1):
+    def __init__(self, degree, n_refines, p1, p2, rank=0, n_ranks=1, rep=(1, 1)):
         self._h = C.c_void_p()
-        rc = lib().pfc_standin_create(degree, n_refines, p1[0], p1[1], p2[0], p2[1], rank, n_ranks,
-                                      C.byref(self._h))
+        rc = lib().pfc_standin_create_ex(degree, n_refines, rep[0], rep[1], p1[0], p1[1], p2[0], p2[1],
+                                         rank, n_ranks, C.byref(self._h))
         if rc != PFC_OK:
             raise PfcError(rc, "pfc_standin_create: invalid arguments")
         self.degree, self.n_refines = degree, n_refines
@@ -401,6 +405,11 @@ class Solver:
         ms, by = C.c_double(), C.c_double()
         self._check(lib().pfc_time_operator(self._h, reps, C.byref(ms), C.byref(by)))
         return ms.value, by.value
+
+    def time_krylov(self, dim, reps=10):
+        a, b, c, d = C.c_double(), C.c_double(), C.c_double(), C.c_double()
+        self._check(lib().pfc_time_krylov(self._h, dim, reps, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        return {"ms_dot": a.value, "bytes_dot": b.value, "ms_axpy": c.value, "bytes_axpy": d.value}
 
     def time_assembly(self, reps=5):
         ms, by = C.c_double(), C.c_double()

@@ -507,3 +507,52 @@ extern "C" int pfc_time_assembly(pfc_handle *h, int32_t reps, double *ms_mean, d
                         (double)P.n_cells * (4.0 * (3 * P.n_s + P.n_s * P.n_s) + 16.0);
   return PFC_OK;
 }
+
+extern "C" int pfc_time_krylov(pfc_handle *h, int32_t dim, int32_t reps, double *ms_dot, double *bytes_dot,
+                               double *ms_axpy, double *bytes_axpy)
+{
+  if (!h || reps < 1 || !ms_dot || !ms_axpy)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->is_setup)
+    return h->fail(PFC_ERR_STATE, "pfc_time_krylov before pfc_setup");
+  if (dim < 1 || dim > h->restart)
+    return h->fail(PFC_ERR_BAD_ARGUMENT, "dim must be in [1, restart]");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  ensure_tab();
+  const Plan &P = h->plan;
+  cudaStream_t s = h->stream;
+  const int64_t n2 = 3 * P.Np / 2;
+  const int grid = vec_grid(h, n2);
+  GmresSmall *g = h->d_small.p;
+  double *V = h->d_V.p, *w = V + (int64_t)dim * h->stride;
+  // neutral control block: state 0, no second pass; coefficients 0 so that w is unchanged
+  PFC_CUDA(h, cudaMemsetAsync(h->d_ctl.p, 0, sizeof(Ctl), s));
+  PFC_CUDA(h, cudaMemsetAsync(g->dots1, 0, sizeof(g->dots1), s));
+  float ms;
+  for (int k = 0; k < 2; ++k)
+    {
+      for (int i = 0; i < 2; ++i) // warm-up
+        if (k == 0)
+          g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0);
+        else
+          g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0);
+      PFC_CUDA(h, cudaEventRecord(h->ev[0], s));
+      for (int i = 0; i < reps; ++i)
+        if (k == 0)
+          g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0);
+        else
+          g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0);
+      h->launches += reps + 2;
+      PFC_CUDA(h, cudaEventRecord(h->ev[1], s));
+      PFC_CUDA(h, cudaStreamSynchronize(s));
+      PFC_CUDA(h, cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]));
+      (k == 0 ? *ms_dot : *ms_axpy) = ms / reps;
+    }
+  PFC_CUDA(h, cudaGetLastError());
+  const double vec = 24.0 * (double)P.Np; // one vector of 3 Np doubles
+  if (bytes_dot)
+    *bytes_dot = (dim + 1) * vec;
+  if (bytes_axpy)
+    *bytes_axpy = (dim + 2) * vec;
+  return PFC_OK;
+}

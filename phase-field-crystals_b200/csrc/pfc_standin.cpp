@@ -75,32 +75,59 @@ double dlag(int p, int k, double x)
 }
 } // namespace
 
+extern "C" int pfc_standin_create_ex(int32_t degree, int32_t n_refines, int32_t rep_x, int32_t rep_y, double x0,
+                                     double y0, double x1, double y1, int32_t rank, int32_t n_ranks,
+                                     pfc_standin **out);
+
 extern "C" int pfc_standin_create(int32_t degree, int32_t n_refines, double x0, double y0, double x1,
                                   double y1, int32_t rank, int32_t n_ranks, pfc_standin **out)
+{
+  return pfc_standin_create_ex(degree, n_refines, 1, 1, x0, y0, x1, y1, rank, n_ranks, out);
+}
+
+// rep_x x rep_y coarse cells (GridGenerator::subdivided_hyper_rectangle; not reachable upstream, where
+// the coarse mesh is one cell): trees in lexicographic order, Morton order inside each tree, which is
+// the order p4est walks its forest.
+extern "C" int pfc_standin_create_ex(int32_t degree, int32_t n_refines, int32_t rep_x, int32_t rep_y, double x0,
+                                     double y0, double x1, double y1, int32_t rank, int32_t n_ranks,
+                                     pfc_standin **out)
 {
   if (!out)
     return PFC_ERR_BAD_ARGUMENT;
   *out = nullptr;
-  if (degree < 1 || degree > 2 || n_refines < 1 || n_refines > 13 || !(x1 > x0) || !(y1 > y0))
+  if (degree < 1 || degree > 2 || n_refines < 1 || n_refines > 13 || !(x1 > x0) || !(y1 > y0) || rep_x < 1 ||
+      rep_y < 1 || rep_x > 64 || rep_y > 64)
     return PFC_ERR_BAD_ARGUMENT;
   if (n_ranks < 1)
     n_ranks = 1;
   if (rank < 0 || rank >= n_ranks)
     return PFC_ERR_BAD_ARGUMENT;
   const int p = degree, ns = (p + 1) * (p + 1), dpc = 3 * ns;
-  const int nx = 1 << n_refines;
-  const int64_t n_cells_g = (int64_t)nx * nx;
+  const int nt = 1 << n_refines; // cells per tree and direction
+  const int nx = rep_x * nt, ny = rep_y * nt;
+  const int64_t cells_per_tree = (int64_t)nt * nt;
+  const int64_t n_cells_g = (int64_t)nx * ny;
+  auto cell_xy = [&](int64_t cell, int &cx, int &cy) {
+    const int64_t tree = cell / cells_per_tree;
+    morton_decode(cell % cells_per_tree, n_refines, cx, cy);
+    cx += (int)(tree % rep_x) * nt;
+    cy += (int)(tree / rep_x) * nt;
+  };
+  auto cell_of = [&](int cx, int cy) {
+    const int64_t tree = (int64_t)(cy / nt) * rep_x + cx / nt;
+    return tree * cells_per_tree + morton_encode(cx % nt, cy % nt, n_refines);
+  };
   if (n_ranks > n_cells_g)
     return PFC_ERR_BAD_ARGUMENT;
-  const int64_t G = (int64_t)p * nx + 1; // fine-grid points per direction
-  const int64_t N = G * G;
+  const int64_t G = (int64_t)p * nx + 1, Gy = (int64_t)p * ny + 1; // fine-grid points per direction
+  const int64_t N = G * Gy;
   pfc_standin *S = new (std::nothrow) pfc_standin();
   if (!S)
     return PFC_ERR_BAD_ARGUMENT;
   S->degree = p;
   S->n_refines = n_refines;
   S->N = N;
-  const double hx = (x1 - x0) / nx, hy = (y1 - y0) / nx;
+  const double hx = (x1 - x0) / nx, hy = (y1 - y0) / ny;
 
   // FE_Q(p) hierarchical local nodes as fine-grid offsets
   int ox[9], oy[9];
@@ -170,7 +197,7 @@ extern "C" int pfc_standin_create(int32_t degree, int32_t n_refines, double x0, 
         while (r + 1 <= n_ranks && cell == chunk_begin(r + 1))
           S->node_offsets[++r] = next;
         int cx, cy;
-        morton_decode(cell, n_refines, cx, cy);
+        cell_xy(cell, cx, cy);
         for (int a = 0; a < ns; ++a)
           {
             const int64_t fx = (int64_t)p * cx + ox[a], fy = (int64_t)p * cy + oy[a];
@@ -189,10 +216,10 @@ extern "C" int pfc_standin_create(int32_t degree, int32_t n_refines, double x0, 
 
   // periodic constraints: x_min -> x_max, y_min -> y_max, corners chain to (x_max, y_max)
   S->node_master.resize(N);
-  for (int64_t fy = 0; fy < G; ++fy)
+  for (int64_t fy = 0; fy < Gy; ++fy)
     for (int64_t fx = 0; fx < G; ++fx)
       {
-        const int64_t mx = fx == 0 ? G - 1 : fx, my = fy == 0 ? G - 1 : fy;
+        const int64_t mx = fx == 0 ? G - 1 : fx, my = fy == 0 ? Gy - 1 : fy;
         S->node_master[id[fy * G + fx]] = id[my * G + mx];
       }
   for (int c = 0; c < 3; ++c)
@@ -220,12 +247,12 @@ extern "C" int pfc_standin_create(int32_t degree, int32_t n_refines, double x0, 
       for (int64_t c = c0; c < c1; ++c)
         {
           int cx, cy;
-          morton_decode(c, n_refines, cx, cy);
+          cell_xy(c, cx, cy);
           for (int dy = -1; dy <= 1; ++dy)
             for (int dx = -1; dx <= 1; ++dx)
               {
-                const int ax = (cx + dx + nx) % nx, ay = (cy + dy + nx) % nx;
-                const int64_t nb = morton_encode(ax, ay, n_refines);
+                const int ax = (cx + dx + nx) % nx, ay = (cy + dy + ny) % ny;
+                const int64_t nb = cell_of(ax, ay);
                 if (mark[nb])
                   continue;
                 bool need = false;
@@ -246,8 +273,8 @@ extern "C" int pfc_standin_create(int32_t degree, int32_t n_refines, double x0, 
       for (int64_t c = 0; c < n_cells_g; ++c)
         {
           int cx, cy;
-          morton_decode(c, n_refines, cx, cy);
-          if (mark[c] || (cx != 0 && cy != 0 && cx != nx - 1 && cy != nx - 1))
+          cell_xy(c, cx, cy);
+          if (mark[c] || (cx != 0 && cy != 0 && cx != nx - 1 && cy != ny - 1))
             continue;
           bool need = false;
           for (int a = 0; a < ns && !need; ++a)
@@ -271,7 +298,7 @@ extern "C" int pfc_standin_create(int32_t degree, int32_t n_refines, double x0, 
   for (int64_t k = 0; k < nc; ++k)
     {
       int cx, cy;
-      morton_decode(cells[k], n_refines, cx, cy);
+      cell_xy(cells[k], cx, cy);
       for (int v = 0; v < 4; ++v)
         {
           S->cell_vertices[k * 8 + v * 2 + 0] = x0 + (cx + (v & 1)) * hx;
