@@ -52,12 +52,16 @@ __device__ __forceinline__ void grid_reduce(double (&acc)[NV], double *partial, 
   __syncthreads();
   if (s_last)
     {
-      if (threadIdx.x < NV)
+      // warp w sums values w, w + 8, ...; its lanes stride over the blocks, then shuffle-reduce:
+      // fixed order, so the result does not depend on which block happened to finish last
+      for (int i = warp; i < NV; i += kVecThreads / 32)
         {
           double s = 0;
-          for (unsigned int b = 0; b < gridDim.x; ++b)
-            s += __ldcg(partial + (size_t)b * kPartialStride + threadIdx.x);
-          out[threadIdx.x] = s;
+          for (unsigned int b = lane; b < gridDim.x; b += 32)
+            s += __ldcg(partial + (size_t)b * kPartialStride + i);
+          s = warp_sum(s);
+          if (lane == 0)
+            out[i] = s;
         }
       if (threadIdx.x == 0)
         *counter = 0;

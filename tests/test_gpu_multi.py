@@ -1,0 +1,28 @@
+"""Multi-GPU parity: N ranks over NCCL == oracle.  Needs >= 2 GPUs (skipped otherwise)."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _n_gpus():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("degree,n_refines,steps,extra", [(1, 5, 2, "{}"), (2, 4, 1, "{}"), (1, 4, 1, '{"use_cuda_graph": 0}')])
+def test_ranks_match_oracle(built, degree, n_refines, steps, extra):
+    n = _n_gpus()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    for world in sorted({2, min(n, 4), min(n, 8)}):
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+               "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.join(ROOT, "tests", "mgpu_worker.py"),
+               str(degree), str(n_refines), str(steps), extra]
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+        print(r.stdout[-3000:])
+        assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
