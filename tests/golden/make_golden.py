@@ -1,0 +1,35 @@
+"""Generates tests/golden/*.npz from the CPU oracle (the reference cannot run here; see oracle/pfc_oracle.h:
+PARITY UNPINNED).  These fixtures pin regressions of the oracle and travel to the GPU box, where the CUDA path
+is compared with them without the oracle being re-run.   python tests/golden/make_golden.py"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "..", "..", "oracle"))
+import oracle as O  # noqa: E402
+
+A = O.LATTICE_A
+
+
+def run(degree, n_refines, steps, disl, name):
+    om = O.Mesh(degree, n_refines, (-6 * A, -5 * A), (6 * A, 5 * A))
+    pos, bur = ([[2 * A, 0], [-2 * A, 0]], [[A, 0], [-A, 0]]) if disl else ((), ())
+    Pn = om.initial_condition(O.default_A0(-0.43, -0.8), -0.43, pos, bur)
+    Pn1 = Pn.copy()
+    its, res = [], []
+    for _ in range(steps):
+        r = om.newton_step(Pn, Pn1, 0.1, 1.0, -0.8)
+        its.append(r["gmres_iters"])
+        res.append(r["residuals"])
+    np.savez_compressed(os.path.join(HERE, name), psi=Pn[:om.N], chi=Pn[om.N:2 * om.N], phi=Pn[2 * om.N:],
+                        gmres_iters=np.array(its[-1]), residuals=np.array(res[-1]),
+                        all_gmres_iters=np.array([sum(i) for i in its]), steps=steps)
+    print(name, its)
+
+
+if __name__ == "__main__":
+    run(1, 6, 1, True, "config1_step1.npz")      # shipped TOML, first timestep
+    run(1, 6, 10, True, "config1_step10.npz")    # shipped TOML, all 10 timesteps (n_timesteps = 10)
+    run(2, 4, 3, True, "q2_r4_step3.npz")

@@ -164,3 +164,27 @@ def test_call_order_errors(built):
     with pytest.raises(built.PfcError):
         built.Solver(dt=-1.0)
     s.close()
+
+
+@pytest.mark.parametrize("name,degree,n_refines", [("config1_step10.npz", 1, 6), ("q2_r4_step3.npz", 2, 4)])
+def test_against_committed_golden(built, name, degree, n_refines):
+    """CUDA path vs tests/golden (oracle output generated by tests/golden/make_golden.py), without the oracle:
+    config 1 = the shipped TOML for all its 10 timesteps."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", name))
+    st = built.StandIn(degree, n_refines, P1, P2)
+    Psi = st.hexagonal_lattice(built.default_A0(PSI0, EPS), PSI0, DISL, BURG)
+    s = built.Solver(degree=degree)
+    s.setup(st)
+    s.set_state(Psi, Psi)
+    tot = []
+    for _ in range(int(g["steps"])):
+        r = s.step()
+        assert r["status"] == 0
+        tot.append(r["gmres_iters_total"])
+    got = s.get_state()
+    N = st.N
+    for k, (a, b) in enumerate(((got[:N], g["psi"]), (got[N:2 * N], g["chi"]), (got[2 * N:], g["phi"]))):
+        assert _rel(a, b) <= 1e-9, (k, _rel(a, b))
+    assert max(abs(int(x) - int(y)) for x, y in zip(tot, g["all_gmres_iters"])) <= 3, (tot, g["all_gmres_iters"])
+    s.close()
