@@ -74,7 +74,8 @@ extern "C" int pfc_create(const pfc_params *p, pfc_handle **out)
       g_create_error = "orthogonalization must be PFC_ORTHO_CGS or PFC_ORTHO_CGS2";
       return PFC_ERR_UNSUPPORTED;
     }
-  if (p->operator_kind != PFC_OPERATOR_ASSEMBLED || p->preconditioner != PFC_PRECOND_NONE)
+  if (p->operator_kind != PFC_OPERATOR_ASSEMBLED ||
+      (p->preconditioner != PFC_PRECOND_NONE && p->preconditioner != PFC_PRECOND_BLOCK_SCHUR) || p->precond_sweeps > 16)
     {
       g_create_error = "operator_kind / preconditioner not available in this build";
       return PFC_ERR_UNSUPPORTED;
@@ -91,6 +92,7 @@ extern "C" int pfc_create(const pfc_params *p, pfc_handle **out)
   h->prm.gmres_n_tmp_vectors = ntmp;
   h->restart = ntmp - 2;
   h->n_basis = ntmp - 1;
+  h->sweeps = p->precond_sweeps > 0 ? p->precond_sweeps : 4;
   int dev = p->device;
   if (dev < 0)
     cudaGetDevice(&dev);
@@ -140,6 +142,7 @@ extern "C" void pfc_destroy(pfc_handle *h)
 }
 
 int launch_assembly(pfc_handle *h, bool const_pass); // pfc_solver.cu
+int precond_after_setup(pfc_handle *h);               // pfc_solver.cu
 
 extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
 {
@@ -218,6 +221,20 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
   PFC_CUDA(h, h->d_small.alloc(1));
   PFC_CUDA(h, h->d_partial.alloc((size_t)kPartialStride * 4096));
   PFC_CUDA(h, h->d_counter.alloc(4));
+  h->eig_valid = false;
+  if (h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR)
+    {
+      h->sstride = (P.Np + P.n_ghost + 15) / 16 * 16;
+      PFC_CUDA(h, h->d_inv_ml.alloc(P.Np));
+      PFC_CUDA(h, h->d_dinvB.alloc(P.Np));
+      PFC_CUDA(h, h->d_pw.alloc((size_t)h->sstride * 9));
+      PFC_CUDA(h, h->d_pv.alloc((size_t)h->sstride * 3));
+      PFC_CUDA(h, h->d_z.alloc(h->stride));
+      PFC_CUDA(h, h->d_u.alloc(h->stride));
+      PFC_CUDA(h, h->d_cheb.alloc(64));
+      for (DevBuf<double> *b : {&h->d_pw, &h->d_pv, &h->d_z, &h->d_u, &h->d_cheb})
+        PFC_CUDA(h, cudaMemsetAsync(b->p, 0, b->n * sizeof(double), s));
+    }
   PFC_CUDA(h, cudaMemsetAsync(h->d_counter.p, 0, 4 * sizeof(unsigned int), s));
   PFC_CUDA(h, cudaMemsetAsync(h->d_ctl.p, 0, sizeof(Ctl), s));
   PFC_CUDA(h, cudaMemsetAsync(h->d_small.p, 0, sizeof(GmresSmall), s));
@@ -239,6 +256,15 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
     {
       h->is_setup = false;
       return rc;
+    }
+  if (h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR)
+    {
+      rc = precond_after_setup(h);
+      if (rc != PFC_OK)
+        {
+          h->is_setup = false;
+          return rc;
+        }
     }
   PFC_CUDA(h, cudaStreamSynchronize(s));
   return PFC_OK;

@@ -221,4 +221,30 @@ int halo_exchange(pfc_handle *h, double *v)
   PFC_NCCL(h, n.GroupEnd());
   return PFC_OK;
 }
+
+int halo_exchange_scalar(pfc_handle *h, double *v)
+{
+  const Plan &P = h->plan;
+  if (P.n_ranks <= 1)
+    return PFC_OK;
+  NcclApi &n = nccl();
+  ncclComm_t comm = (ncclComm_t)h->comm;
+  const int64_t ns = (int64_t)P.send_rows.size();
+  if (ns > 0)
+    {
+      halo_pack1_kernel<<<(int)((ns + 255) / 256), 256, 0, h->stream>>>(h->d_send_buf.p, v, h->d_send_rows.p, ns);
+      h->launches++;
+    }
+  PFC_NCCL(h, n.GroupStart());
+  for (size_t p = 0; p < P.peers.size(); ++p)
+    {
+      const int64_t nr = P.recv_ptr[p + 1] - P.recv_ptr[p], nsd = P.send_ptr[p + 1] - P.send_ptr[p];
+      if (nsd > 0)
+        PFC_NCCL(h, n.Send(h->d_send_buf.p + P.send_ptr[p], (size_t)nsd, ncclDouble, P.peers[p], comm, h->stream));
+      if (nr > 0)
+        PFC_NCCL(h, n.Recv(v + P.Np + P.recv_ptr[p], (size_t)nr, ncclDouble, P.peers[p], comm, h->stream));
+    }
+  PFC_NCCL(h, n.GroupEnd());
+  return PFC_OK;
+}
 } // namespace pfc

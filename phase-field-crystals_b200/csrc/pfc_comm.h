@@ -13,5 +13,6 @@ namespace pfc
 void comm_destroy(pfc_handle *h);
 int comm_exchange_send_lists(pfc_handle *h);           // after build_plan: fills plan.send_ptr / send_rows
 int halo_exchange(pfc_handle *h, double *v);           // v's ghost tail := owners' values (stream-ordered)
+int halo_exchange_scalar(pfc_handle *h, double *v);    // scalar field [owned Np | ghosts]
 int allreduce_sum(pfc_handle *h, double *dev, size_t n); // in place, stream-ordered; no-op on one rank
 } // namespace pfc

@@ -7,7 +7,7 @@
 #include <string>
 #include <vector>
 
-#include "pfc_krylov.cuh"
+#include "pfc_precond.cuh"
 #include "pfc_plan.h"
 
 struct ncclComm;
@@ -76,12 +76,21 @@ struct pfc_handle
   pfc::Ctl *h_ctl = nullptr; // pinned
   double *h_scalar = nullptr; // pinned [4]
   cudaGraphExec_t cycle_graph[2] = {nullptr, nullptr}; // [first cycle (x = 0), later cycles]
+  int64_t graph_launches[2] = {0, 0};
 
   // multi-GPU
   ncclComm *comm = nullptr;
   int comm_rank = 0, comm_size = 1;
   pfc::DevBuf<int32_t> d_send_rows;
   pfc::DevBuf<double> d_send_buf;
+
+  // block-Schur preconditioner (pfc_precond.cuh)
+  int64_t sstride = 0;                    // doubles between scalar work vectors (Np + n_ghost, rounded to 16)
+  pfc::DevBuf<double> d_inv_ml, d_dinvB, d_pw, d_z, d_u, d_cheb, d_pv;
+  int sweeps = 4;
+  double eig_min = 0, eig_max = 0;
+  bool eig_valid = false;
+  int solves_since_eig = 0;
 
   int64_t launches = 0;
 

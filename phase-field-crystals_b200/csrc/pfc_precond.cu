@@ -1,0 +1,208 @@
+// pfc_precond.cu — host drivers of the block-Schur right preconditioner (kernels: pfc_precond.cuh).
+#include <algorithm>
+#include <cmath>
+#include <vector>
+
+#include "pfc_comm.h"
+#include "pfc_handle.h"
+
+using namespace pfc;
+
+#define PFC_TRY(expr)    \
+  do                     \
+    {                    \
+      int rc_ = (expr);  \
+      if (rc_ != PFC_OK) \
+        return rc_;      \
+    }                    \
+  while (0)
+
+static SellArgs sell_args(const pfc_handle *h)
+{
+  SellArgs S;
+  S.slice_ptr = h->d_slice_ptr.p;
+  S.col = h->d_col.p;
+  S.B = h->d_B.p;
+  S.C = h->d_C.p;
+  S.M = h->d_M.p;
+  S.K = h->d_K.p;
+  S.Np = h->plan.Np;
+  S.n_slices = h->plan.n_slices;
+  S.dtth = h->prm.dt * h->prm.theta;
+  return S;
+}
+
+static inline int sell_blocks(const pfc_handle *h)
+{
+  return (int)((h->plan.n_slices * 32 + kSpmvThreads - 1) / kSpmvThreads);
+}
+static inline int vgrid(const pfc_handle *h, int64_t n)
+{
+  return (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, (int64_t)h->n_sm * 8));
+}
+
+// work vectors inside d_pw
+enum { W_M1 = 0, W_T, W_RHS, W_XA, W_XB, W_D, W_T1, W_T2, W_CHI };
+static inline double *wv(const pfc_handle *h, int k) { return h->d_pw.p + (int64_t)k * h->sstride; }
+
+// lumped mass: inv_ml = 1 / rowsum(M); M is iterate independent (assembled once in pfc_setup)
+int precond_after_setup(pfc_handle *h)
+{
+  rowdiag_kernel<true><<<sell_blocks(h), kSpmvThreads, 0, h->stream>>>(sell_args(h), h->d_inv_ml.p);
+  h->launches++;
+  PFC_CUDA(h, cudaGetLastError());
+  // deterministic start vector of the power iterations: zero on constrained / padding rows
+  const Plan &P = h->plan;
+  std::vector<double> v((size_t)h->sstride * 3, 0.0);
+  for (int64_t r = 0; r < P.Np; ++r)
+    if (P.perm[r] >= 0 && P.row_master[r] == r)
+      {
+        const uint64_t g = (uint64_t)P.perm[r] * 0x9E3779B97F4A7C15ull;
+        v[r] = 0.5 + (double)((g >> 40) & 0xFFFF) / 65536.0;            // for lambda_max
+        v[h->sstride + r] = ((g >> 20) & 1) ? 1.0 : -1.0;               // rough start for the other end
+      }
+  PFC_CUDA(h, cudaMemcpyAsync(h->d_pv.p, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+  h->eig_valid = false;
+  return PFC_OK;
+}
+
+// y = diag(B)^-1 S_L v   (scalar fields), the operator whose spectrum the Chebyshev interval must cover
+static int apply_dinv_SL(pfc_handle *h, double *v, double *y)
+{
+  const SellArgs S = sell_args(h);
+  const int nb = sell_blocks(h);
+  cudaStream_t s = h->stream;
+  double *t1 = wv(h, W_T1), *t2 = wv(h, W_T2);
+  PFC_TRY(halo_exchange_scalar(h, v));
+  kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, nullptr, 0.0, v, 1.0, h->d_inv_ml.p, t1, nullptr, nullptr);
+  PFC_TRY(halo_exchange_scalar(h, t1));
+  kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, nullptr, 0.0, t1, 1.0, h->d_inv_ml.p, t2, nullptr, nullptr);
+  PFC_TRY(halo_exchange_scalar(h, t2));
+  bcd_kernel<2><<<nb, kSpmvThreads, 0, s>>>(S, v, t1, t2, 1.0, -1.0, 1.0, nullptr, h->d_dinvB.p, nullptr, nullptr, y, nullptr);
+  h->launches += 3;
+  return PFC_OK;
+}
+
+static int scalar_norm(pfc_handle *h, const double *v, double *out)
+{
+  const int64_t n2 = h->plan.Np / 2;
+  GmresSmall *g = h->d_small.p;
+  multidot_kernel<0><<<vgrid(h, n2), kVecThreads, 0, h->stream>>>(nullptr, 0, v, n2, h->d_partial.p, &g->nrm2[0],
+                                                                  h->d_counter.p, nullptr, 0);
+  h->launches++;
+  PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1));
+  PFC_CUDA(h, cudaMemcpyAsync(h->h_scalar, &g->nrm2[0], sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+  *out = std::sqrt(h->h_scalar[0]);
+  return PFC_OK;
+}
+
+// after every assembly of B: Jacobi scaling; every few solves: spectrum bounds by (shifted) power iteration,
+// warm-started from the previous vectors; then the Chebyshev coefficients.
+int precond_refresh(pfc_handle *h)
+{
+  const Plan &P = h->plan;
+  cudaStream_t s = h->stream;
+  rowdiag_kernel<false><<<sell_blocks(h), kSpmvThreads, 0, s>>>(sell_args(h), h->d_dinvB.p);
+  h->launches++;
+  const bool estimate = !h->eig_valid || h->solves_since_eig >= 16;
+  if (estimate)
+    {
+      const int iters = h->eig_valid ? 8 : 30;
+      double *v = h->d_pv.p, *v2 = h->d_pv.p + h->sstride, *y = h->d_pv.p + 2 * h->sstride;
+      double lam = 0, nv = 0;
+      const int g = vgrid(h, P.Np);
+      for (int pass = 0; pass < 2; ++pass)
+        {
+          double *x = pass == 0 ? v : v2;
+          PFC_TRY(scalar_norm(h, x, &nv));
+          if (!(nv > 0))
+            return h->fail(PFC_ERR_NONFINITE, "preconditioner: zero power-iteration vector");
+          vec_mul_kernel<<<g, 256, 0, s>>>(x, nullptr, 1.0 / nv, nullptr, x, nullptr, P.Np, nullptr);
+          double mu = 0;
+          for (int it = 0; it < iters; ++it)
+            {
+              PFC_TRY(apply_dinv_SL(h, x, y));
+              if (pass == 1) // shifted operator lam_max I - A: dominant eigenvalue lam_max - lam_min
+                vec_axpby_kernel<<<g, 256, 0, s>>>(y, lam, x, -1.0, y, P.Np);
+              PFC_TRY(scalar_norm(h, y, &mu));
+              if (!std::isfinite(mu) || !(mu > 0))
+                return h->fail(PFC_ERR_NONFINITE, "preconditioner: power iteration broke down");
+              vec_mul_kernel<<<g, 256, 0, s>>>(x, nullptr, 1.0 / mu, nullptr, y, nullptr, P.Np, nullptr);
+              h->launches += 2;
+            }
+          if (pass == 0)
+            lam = 1.1 * mu; // power iteration converges from below: safety margin
+          else
+            {
+              h->eig_max = lam;
+              h->eig_min = std::max(0.85 * (lam - mu), lam / 200.0);
+            }
+        }
+      h->eig_valid = true;
+      h->solves_since_eig = 0;
+      // Chebyshev coefficients for steps 1 .. sweeps-1 (step 0 is x = dinv r / theta)
+      const double theta = 0.5 * (h->eig_max + h->eig_min), delta = 0.5 * (h->eig_max - h->eig_min);
+      std::vector<double> c(64, 0.0);
+      const double sigma = theta / delta;
+      double rho = 1.0 / sigma;
+      c[0] = 1.0 / theta;
+      for (int i = 1; i < h->sweeps; ++i)
+        {
+          const double rho_new = 1.0 / (2.0 * sigma - rho);
+          c[2 * i] = rho_new * rho;
+          c[2 * i + 1] = 2.0 * rho_new / delta;
+          rho = rho_new;
+        }
+      PFC_CUDA(h, cudaMemcpyAsync(h->d_cheb.p, c.data(), 64 * sizeof(double), cudaMemcpyHostToDevice, s));
+      PFC_CUDA(h, cudaStreamSynchronize(s));
+    }
+  h->solves_since_eig++;
+  PFC_CUDA(h, cudaGetLastError());
+  return PFC_OK;
+}
+
+// out = P^-1 in   (in, out: solver vectors of 3 components; stream-ordered, graph-capturable)
+int precond_apply(pfc_handle *h, const double *in, double *out, const Ctl *ctl)
+{
+  const Plan &P = h->plan;
+  const SellArgs S = sell_args(h);
+  const int nb = sell_blocks(h), g = vgrid(h, P.Np);
+  cudaStream_t s = h->stream;
+  const int64_t Np = P.Np;
+  const double *r0 = in, *r1 = in + Np, *r2 = in + 2 * Np;
+  double *m1 = wv(h, W_M1), *t = wv(h, W_T), *rhs = wv(h, W_RHS), *xa = wv(h, W_XA), *xb = wv(h, W_XB);
+  double *d = wv(h, W_D), *t1 = wv(h, W_T1), *t2 = wv(h, W_T2), *chi = wv(h, W_CHI);
+  const double *iml = h->d_inv_ml.p;
+
+  vec_mul_kernel<<<g, 256, 0, s>>>(m1, nullptr, 1.0, nullptr, r1, iml, Np, ctl);                     // m1 = M_L^-1 r1
+  PFC_TRY(halo_exchange_scalar(h, m1));
+  kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, r2, 1.0, m1, -1.0, iml, t, nullptr, ctl);                // t = M_L^-1 (r2 - K m1)
+  PFC_TRY(halo_exchange_scalar(h, t));
+  bcd_kernel<0><<<nb, kSpmvThreads, 0, s>>>(S, nullptr, m1, t, 0.0, -1.0, -1.0, r0, nullptr, nullptr, nullptr, rhs, ctl);
+  // Chebyshev on S_L psi = rhs, Jacobi scaling diag(B)^-1
+  vec_mul_kernel<<<g, 256, 0, s>>>(d, xa, 1.0, h->d_cheb.p, rhs, h->d_dinvB.p, Np, ctl);            // d = x = dinv rhs / theta
+  h->launches += 4;
+  double *x = xa, *xn = xb;
+  for (int i = 1; i < h->sweeps; ++i)
+    {
+      PFC_TRY(halo_exchange_scalar(h, x));
+      kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, nullptr, 0.0, x, 1.0, iml, t1, nullptr, ctl);
+      PFC_TRY(halo_exchange_scalar(h, t1));
+      kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, nullptr, 0.0, t1, 1.0, iml, t2, nullptr, ctl);
+      PFC_TRY(halo_exchange_scalar(h, t2));
+      bcd_kernel<1><<<nb, kSpmvThreads, 0, s>>>(S, x, t1, t2, 1.0, -1.0, 1.0, rhs, h->d_dinvB.p, d, h->d_cheb.p + 2 * i, xn, ctl);
+      std::swap(x, xn);
+      h->launches += 3;
+    }
+  // back substitution; psi -> out[0], chi -> out[1], phi -> out[2]
+  PFC_TRY(halo_exchange_scalar(h, x));
+  kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, r1, 1.0, x, -1.0, iml, chi, out + Np, ctl);              // chi = M_L^-1 (r1 - K psi)
+  PFC_TRY(halo_exchange_scalar(h, chi));
+  kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, r2, 1.0, chi, -1.0, iml, out + 2 * Np, nullptr, ctl);    // phi = M_L^-1 (r2 - K chi)
+  vec_mul_kernel<<<g, 256, 0, s>>>(out, nullptr, 1.0, nullptr, x, nullptr, Np, ctl);
+  h->launches += 3;
+  PFC_CUDA(h, cudaGetLastError());
+  return PFC_OK;
+}

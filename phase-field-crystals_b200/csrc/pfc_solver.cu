@@ -42,6 +42,9 @@ static void launch_asm_colors(pfc_handle *h, const AsmArgs &A)
     }
 }
 
+int precond_refresh(pfc_handle *h);                                                    // pfc_precond.cu
+int precond_apply(pfc_handle *h, const double *in, double *out, const pfc::Ctl *ctl); // pfc_precond.cu
+
 int launch_assembly(pfc_handle *h, bool const_pass)
 {
   const Plan &P = h->plan;
@@ -165,6 +168,7 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle)
   double *partial = h->d_partial.p;
   unsigned int *cnt = h->d_counter.p;
   const int always = h->prm.orthogonalization == PFC_ORTHO_CGS2 ? 1 : 0;
+  const bool precond = h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR;
 
   // v0 = b - A x ; rho = ||v0|| ; check ; v0 /= rho          ([dealii-ext] start of the outer loop)
   if (!first_cycle)
@@ -180,7 +184,13 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle)
     {
       const int dim = inner + 1;
       double *w = V + (int64_t)dim * st;
-      PFC_TRY(apply_operator(h, V + (int64_t)inner * st, w, ctl)); // A.vmult
+      if (precond)
+        { // right preconditioning: w = J P^-1 v_inner
+          PFC_TRY(precond_apply(h, V + (int64_t)inner * st, h->d_z.p, ctl));
+          PFC_TRY(apply_operator(h, h->d_z.p, w, ctl));
+        }
+      else
+        PFC_TRY(apply_operator(h, V + (int64_t)inner * st, w, ctl)); // A.vmult
       g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots0, cnt, ctl, 0);
       PFC_TRY(allreduce_sum(h, g->dots0, dim + 1));
       g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots0, partial, &g->nrm2[0], cnt, ctl, 0);
@@ -195,7 +205,16 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle)
       h->launches += 7;
     }
   backsolve_kernel<<<1, 1, 0, s>>>(g, ctl);
-  xupdate_kernel<<<grid, kVecThreads, 0, s>>>(V, st, h->d_x.p, n2, g, ctl);
+  if (precond)
+    { // x += P^-1 (V y)
+      PFC_CUDA(h, cudaMemsetAsync(h->d_u.p, 0, h->d_u.n * sizeof(double), s));
+      xupdate_kernel<<<grid, kVecThreads, 0, s>>>(V, st, h->d_u.p, n2, g, ctl);
+      PFC_TRY(precond_apply(h, h->d_u.p, h->d_z.p, nullptr));
+      axpy1_kernel<<<grid, kVecThreads, 0, s>>>(h->d_x.p, h->d_z.p, 3 * P.Np);
+      h->launches++;
+    }
+  else
+    xupdate_kernel<<<grid, kVecThreads, 0, s>>>(V, st, h->d_x.p, n2, g, ctl);
   h->launches += 2;
   PFC_CUDA(h, cudaMemcpyAsync(h->h_ctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s));
   PFC_CUDA(h, cudaGetLastError());
@@ -223,11 +242,11 @@ static int run_cycle(pfc_handle *h, bool first_cycle)
       PFC_CUDA(h, e);
       PFC_CUDA(h, cudaGraphInstantiate(&h->cycle_graph[gi], graph, 0));
       cudaGraphDestroy(graph);
-      h->launches = before; // capture launched nothing
+      h->graph_launches[gi] = h->launches - before; // kernel nodes recorded in the graph
+      h->launches = before;                          // capture launched nothing
     }
   PFC_CUDA(h, cudaGraphLaunch(h->cycle_graph[gi], h->stream));
-  // kernels inside one cycle (see enqueue_cycle); halo packs excluded
-  h->launches += 3 + (first_cycle ? 0 : 1) + (int64_t)h->restart * 8 + 2;
+  h->launches += h->graph_launches[gi];
   return PFC_OK;
 }
 
@@ -314,6 +333,8 @@ extern "C" int pfc_solve_update(pfc_handle *h, int64_t *gmres_iters, double *fin
     return h->fail(PFC_ERR_STATE, "pfc_solve_update before pfc_assemble");
   PFC_CUDA(h, cudaSetDevice(h->device));
   const Plan &P = h->plan;
+  if (h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR)
+    PFC_TRY(precond_refresh(h));
   PFC_TRY(gmres_solve(h, gmres_iters, final_residual));
   // constraints.distribute(dPsi_n) (mpi.cpp:485); Psi_n += dPsi_n (mpi.cpp:487-491)
   PFC_TRY(halo_exchange(h, h->d_x.p));

@@ -80,6 +80,10 @@ def test_gmres_solve_matches_oracle(built, degree, n_refines):
     (1, 6, 2, {"use_cuda_graph": 0}),
     (2, 4, 2, {}),
     (1, 4, 2, {"theta": 0.5}),
+    (1, 6, 3, {"preconditioner": 1}),                # block-Schur right preconditioner, same stopping rule
+    (2, 4, 2, {"preconditioner": 1}),
+    (2, 4, 2, {"preconditioner": 1, "precond_sweeps": 6, "use_cuda_graph": 0}),
+    (1, 5, 2, {"preconditioner": 1, "theta": 0.5}),
 ])
 def test_step_parity(built, degree, n_refines, n_steps, kw):
     theta = kw.get("theta", 1.0)
