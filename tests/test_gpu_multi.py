@@ -14,7 +14,8 @@ def _n_gpus():
     return torch.cuda.device_count()
 
 
-@pytest.mark.parametrize("degree,n_refines,steps,extra", [(1, 5, 2, "{}"), (2, 4, 1, "{}"), (1, 4, 1, '{"use_cuda_graph": 0}')])
+@pytest.mark.parametrize("degree,n_refines,steps,extra", [(1, 5, 2, "{}"), (2, 4, 1, "{}"), (1, 4, 1, '{"use_cuda_graph": 0}'),
+                                                          (1, 5, 2, '{"preconditioner": 1}'), (2, 4, 1, '{"preconditioner": 1}')])
 def test_ranks_match_oracle(built, degree, n_refines, steps, extra):
     n = _n_gpus()
     if n < 2:
