@@ -74,7 +74,7 @@ extern "C" int pfc_create(const pfc_params *p, pfc_handle **out)
       g_create_error = "orthogonalization must be PFC_ORTHO_CGS or PFC_ORTHO_CGS2";
       return PFC_ERR_UNSUPPORTED;
     }
-  if (p->operator_kind != PFC_OPERATOR_ASSEMBLED ||
+  if ((p->operator_kind != PFC_OPERATOR_ASSEMBLED && p->operator_kind != PFC_OPERATOR_MATRIX_FREE) ||
       (p->preconditioner != PFC_PRECOND_NONE && p->preconditioner != PFC_PRECOND_BLOCK_SCHUR) || p->precond_sweeps > 16)
     {
       g_create_error = "operator_kind / preconditioner not available in this build";
@@ -179,6 +179,7 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
   PFC_CUDA(h, h->d_cell_row.upload(P.cell_row, s));
   PFC_CUDA(h, h->d_cell_pos.upload(P.cell_pos, s));
   PFC_CUDA(h, h->d_cell_spos.upload(P.cell_spos, s));
+  PFC_CUDA(h, h->d_cell_col.upload(P.cell_col, s));
   PFC_CUDA(h, h->d_cell_h.upload(P.cell_h, s));
   PFC_CUDA(h, h->d_col.upload(P.col, s));
   PFC_CUDA(h, h->d_slice_ptr.upload(P.slice_ptr, s));

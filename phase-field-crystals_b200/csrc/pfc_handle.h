@@ -63,7 +63,7 @@ struct pfc_handle
   int restart = 0;    // n_tmp_vectors - 2
 
   // mesh tables
-  pfc::DevBuf<int32_t> d_cell_gather, d_cell_row, d_cell_pos, d_cell_spos, d_col, d_slave, d_slave_master;
+  pfc::DevBuf<int32_t> d_cell_gather, d_cell_row, d_cell_pos, d_cell_spos, d_cell_col, d_col, d_slave, d_slave_master;
   pfc::DevBuf<double> d_cell_h, d_tab;
   pfc::DevBuf<int64_t> d_slice_ptr, d_api_map;
   // matrix blocks (SELL entry order) and vectors
@@ -75,8 +75,8 @@ struct pfc_handle
   pfc::DevBuf<unsigned int> d_counter;
   pfc::Ctl *h_ctl = nullptr; // pinned
   double *h_scalar = nullptr; // pinned [4]
-  cudaGraphExec_t cycle_graph[2] = {nullptr, nullptr}; // [first cycle (x = 0), later cycles]
-  int64_t graph_launches[2] = {0, 0};
+  cudaGraphExec_t cycle_graph[4] = {nullptr, nullptr, nullptr, nullptr}; // [first cycle (x = 0), later] x [one, two GS passes]
+  int64_t graph_launches[4] = {0, 0, 0, 0};
 
   // multi-GPU
   ncclComm *comm = nullptr;

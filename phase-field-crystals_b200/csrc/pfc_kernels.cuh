@@ -47,6 +47,7 @@ struct AsmArgs
   const double *tab; // shape[nq][ns], dshape[nq][ns][2], qw[nq]
   int64_t Np;
   double dt, theta, eps;
+  int rhs_only; // matrix-free operator: only -R is needed, B and C are not stored
 };
 
 constexpr int kAsmThreads = 128;
@@ -174,6 +175,7 @@ static __global__ void __launch_bounds__(kAsmThreads) assemble_kernel(AsmArgs A,
           r1 += ni * cf[3] - (gix * cf[4] + giy * cf[5]);
           r2 += ni * cf[6] - (gix * cf[7] + giy * cf[8]);
           const double bm = cf[9], bx = cf[10], by = cf[11], cm = cf[12];
+          if (!A.rhs_only)
 #pragma unroll
           for (int j = 0; j < NS; ++j)
             {
@@ -196,6 +198,7 @@ static __global__ void __launch_bounds__(kAsmThreads) assemble_kernel(AsmArgs A,
           A.rhs[A.Np + row] += r1;
           A.rhs[2 * A.Np + row] += r2;
         }
+      if (CONST_PASS || !A.rhs_only)
 #pragma unroll
       for (int j = 0; j < NS; ++j)
         {
@@ -206,7 +209,7 @@ static __global__ void __launch_bounds__(kAsmThreads) assemble_kernel(AsmArgs A,
     }
   // constrained local row: |local(i,i)| on the slave's own diagonal ([dealii-ext])
   const int32_t sp = A.cell_spos[cell * NS + i];
-  if (sp >= 0)
+  if (sp >= 0 && (CONST_PASS || !A.rhs_only))
     d0[sp] += fabs(m0[i]);
 }
 

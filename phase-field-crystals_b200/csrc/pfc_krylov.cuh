@@ -76,7 +76,8 @@ static __global__ void __launch_bounds__(kVecThreads) multidot_kernel(const doub
                                                                double *partial, double *out,
                                                                unsigned int *counter, const Ctl *ctl, int pass)
 {
-  if (ctl && (ctl->state != 0 || (pass == 1 && ctl->reorth == 0)))
+  (void)pass;
+  if (ctl && ctl->state != 0)
     return;
   double acc[DIM + 1];
 #pragma unroll
@@ -106,7 +107,8 @@ static __global__ void __launch_bounds__(kVecThreads) multiaxpy_kernel(const dou
                                                                 double *out, unsigned int *counter, Ctl *ctl,
                                                                 int pass)
 {
-  if (ctl->state != 0 || (pass == 1 && ctl->reorth == 0))
+  (void)pass;
+  if (ctl->state != 0)
     return;
   double hh[DIM];
 #pragma unroll
@@ -140,39 +142,31 @@ struct GmresSmall
   double nrm2[2];                  // ||w||^2 after pass 0 / pass 1
 };
 
-// after pass 0: record ||w||^2 before, decide on the second pass (Kelley test / always)
-static __global__ void ortho_decide_kernel(GmresSmall *g, Ctl *ctl, int dim, int always)
+// Hessenberg column, Givens rotation, residual estimate, SolverControl::check.
+// two_pass: the iteration ran both Gram-Schmidt passes (PFC_ORTHO_CGS2, or after a Kelley trip).
+// Otherwise the Kelley test [dealii-ext: norm_vv > 10 * norm_vv_start * sqrt(eps)] is applied to the single
+// pass; if it trips, the iteration is discarded and the cycle ends with state 3: the host continues the
+// solve with two-pass cycles (the re-orthogonalisation flag is sticky, as in deal.II).
+static __global__ void givens_kernel(GmresSmall *g, Ctl *ctl, int inner, int two_pass)
 {
   if (ctl->state != 0)
     return;
-  ctl->ww0 = g->dots0[dim];
-  ctl->pass1 = 0;
-  if (always)
-    ctl->reorth = 1;
-  else if (ctl->reorth == 0)
+  const int dim = inner + 1;
+  if (!two_pass)
     {
-      // [dealii-ext] norm_vv > 10 * norm_vv_start * sqrt(eps) keeps the single pass
       const double before = sqrt(g->dots0[dim]), after = sqrt(g->nrm2[0]);
       if (!(after > 10.0 * before * sqrt(2.220446049250313e-16)))
         {
           ctl->reorth = 1;
           ctl->kelley_trips++;
+          ctl->state = 3;
+          return;
         }
     }
-  if (ctl->reorth)
-    ctl->pass1 = 1;
-}
-
-// Hessenberg column, Givens rotation, residual estimate, SolverControl::check
-static __global__ void givens_kernel(GmresSmall *g, Ctl *ctl, int inner)
-{
-  if (ctl->state != 0)
-    return;
-  const int dim = inner + 1;
   double h[kMaxBasis + 1];
   for (int i = 0; i < dim; ++i)
-    h[i] = g->dots0[i] + (ctl->pass1 ? g->dots1[i] : 0.0);
-  const double s = sqrt(ctl->pass1 ? g->nrm2[1] : g->nrm2[0]);
+    h[i] = g->dots0[i] + (two_pass ? g->dots1[i] : 0.0);
+  const double s = sqrt(two_pass ? g->nrm2[1] : g->nrm2[0]);
   h[dim] = s;
   ctl->inv_norm = (s != 0.0) ? 1.0 / s : 1.0;
   for (int i = 0; i < inner; ++i)

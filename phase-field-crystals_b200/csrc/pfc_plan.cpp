@@ -389,6 +389,7 @@ int build_plan(const pfc_mesh &m, int degree, Plan &P)
   P.cell_gather.resize((size_t)m.n_cells * ns);
   P.cell_row.resize((size_t)m.n_cells * ns);
   P.cell_spos.resize((size_t)m.n_cells * ns);
+  P.cell_col.resize((size_t)m.n_cells * ns);
   P.cell_pos.resize((size_t)m.n_cells * ns * ns);
   P.cell_h.resize((size_t)m.n_cells * 2);
   int bad_pos = 0;
@@ -411,6 +412,9 @@ int build_plan(const pfc_mesh &m, int degree, Plan &P)
           const bool row_owned = owned(mt);
           const int32_t r = row_owned ? g2l[mt] : -1;
           P.cell_row[k * ns + a] = r;
+          P.cell_col[k * ns + a] = g2l[mt];
+          if (g2l[mt] < 0)
+            bad_pos++;
           P.cell_spos[k * ns + a] = (mt != t && owned(t)) ? entry_pos(g2l[t], t) : -1;
           if (mt != t && owned(t) && P.cell_spos[k * ns + a] < 0)
             bad_pos++;

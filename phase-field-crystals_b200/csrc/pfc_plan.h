@@ -50,6 +50,7 @@ struct Plan
   std::vector<int32_t> cell_gather; // [n_cells][n_s] internal id of the raw node (state gather)
   std::vector<int32_t> cell_row;    // [n_cells][n_s] internal row of the resolved node, -1 if not owned
   std::vector<int32_t> cell_pos;    // [n_cells][n_s][n_s] entry position of (m(a), m(b)), -1 if row not owned
+  std::vector<int32_t> cell_col;    // [n_cells][n_s] internal id of the resolved node (matrix-free column gather)
   std::vector<int32_t> cell_spos;   // [n_cells][n_s] entry position of the slave diagonal, -1 if not slave/owned
   std::vector<double>  cell_h;      // [n_cells][2] hx, hy
   // reference tables

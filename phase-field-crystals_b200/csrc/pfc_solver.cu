@@ -6,6 +6,7 @@
 
 #include "pfc_comm.h"
 #include "pfc_handle.h"
+#include "pfc_matfree.cuh"
 
 using namespace pfc;
 
@@ -66,6 +67,9 @@ int launch_assembly(pfc_handle *h, bool const_pass)
   A.dt = h->prm.dt;
   A.theta = h->prm.theta;
   A.eps = h->prm.eps;
+  // matrix-free operator without preconditioner: B and C are never read
+  A.rhs_only = (!const_pass && h->prm.operator_kind == PFC_OPERATOR_MATRIX_FREE &&
+                h->prm.preconditioner == PFC_PRECOND_NONE) ? 1 : 0;
   cudaStream_t s = h->stream;
   if (const_pass)
     {
@@ -111,10 +115,42 @@ static int launch_spmv(pfc_handle *h, const double *x, double *y, const Ctl *ctl
   return PFC_OK;
 }
 
+// matrix-free y = J x: zero y, then one launch per colour (pfc_matfree.cuh)
+template <int NS>
+static int launch_mf(pfc_handle *h, const double *x, double *y, const Ctl *ctl)
+{
+  const Plan &P = h->plan;
+  MfArgs A;
+  A.cell_gather = h->d_cell_gather.p;
+  A.cell_col = h->d_cell_col.p;
+  A.cell_row = h->d_cell_row.p;
+  A.cell_spos = h->d_cell_spos.p;
+  A.cell_h = h->d_cell_h.p;
+  A.psi_n = h->d_psi_n.p;
+  A.tab = h->d_tab.p;
+  A.Np = P.Np;
+  A.dtth = h->prm.dt * h->prm.theta;
+  A.eps = h->prm.eps;
+  PFC_CUDA(h, cudaMemsetAsync(y, 0, 3 * P.Np * sizeof(double), h->stream));
+  constexpr int cells_per_block = (32 / NS) * (kAsmThreads / 32);
+  for (int c = 0; c < P.n_colors; ++c)
+    {
+      const int64_t b = P.color_ptr[c], e = P.color_ptr[c + 1];
+      if (e <= b)
+        continue;
+      const int blocks = (int)((e - b + cells_per_block - 1) / cells_per_block);
+      mf_apply_kernel<NS><<<blocks, kAsmThreads, 0, h->stream>>>(A, x, y, b, e, ctl);
+      h->launches++;
+    }
+  return PFC_OK;
+}
+
 // y = J x with the halo of x refreshed first (multi-rank)
 static int apply_operator(pfc_handle *h, double *x, double *y, const Ctl *ctl)
 {
   PFC_TRY(halo_exchange(h, x));
+  if (h->prm.operator_kind == PFC_OPERATOR_MATRIX_FREE)
+    return h->plan.n_s == 4 ? launch_mf<4>(h, x, y, ctl) : launch_mf<9>(h, x, y, ctl);
   return launch_spmv(h, x, y, ctl);
 }
 
@@ -154,7 +190,7 @@ static void ensure_tab()
 }
 
 // ---- one restart cycle, enqueued on the stream (captured into a CUDA graph when enabled) -----------
-static int enqueue_cycle(pfc_handle *h, bool first_cycle)
+static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass)
 {
   ensure_tab();
   const Plan &P = h->plan;
@@ -167,7 +203,6 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle)
   const int64_t st = h->stride;
   double *partial = h->d_partial.p;
   unsigned int *cnt = h->d_counter.p;
-  const int always = h->prm.orthogonalization == PFC_ORTHO_CGS2 ? 1 : 0;
   const bool precond = h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR;
 
   // v0 = b - A x ; rho = ||v0|| ; check ; v0 /= rho          ([dealii-ext] start of the outer loop)
@@ -195,14 +230,17 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle)
       PFC_TRY(allreduce_sum(h, g->dots0, dim + 1));
       g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots0, partial, &g->nrm2[0], cnt, ctl, 0);
       PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1));
-      ortho_decide_kernel<<<1, 1, 0, s>>>(g, ctl, dim, always);
-      g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots1, cnt, ctl, 1);
-      PFC_TRY(allreduce_sum(h, g->dots1, dim + 1));
-      g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots1, partial, &g->nrm2[1], cnt, ctl, 1);
-      PFC_TRY(allreduce_sum(h, &g->nrm2[1], 1));
-      givens_kernel<<<1, 1, 0, s>>>(g, ctl, inner);
+      if (two_pass)
+        {
+          g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots1, cnt, ctl, 1);
+          PFC_TRY(allreduce_sum(h, g->dots1, dim + 1));
+          g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots1, partial, &g->nrm2[1], cnt, ctl, 1);
+          PFC_TRY(allreduce_sum(h, &g->nrm2[1], 1));
+          h->launches += 2;
+        }
+      givens_kernel<<<1, 1, 0, s>>>(g, ctl, inner, two_pass ? 1 : 0);
       scale_kernel<<<grid, kVecThreads, 0, s>>>(w, n2, ctl);
-      h->launches += 7;
+      h->launches += 5;
     }
   backsolve_kernel<<<1, 1, 0, s>>>(g, ctl);
   if (precond)
@@ -221,17 +259,17 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle)
   return PFC_OK;
 }
 
-static int run_cycle(pfc_handle *h, bool first_cycle)
+static int run_cycle(pfc_handle *h, bool first_cycle, bool two_pass)
 {
-  const int gi = first_cycle ? 0 : 1;
+  const int gi = (first_cycle ? 0 : 1) + (two_pass ? 2 : 0);
   if (!h->prm.use_cuda_graph)
-    return enqueue_cycle(h, first_cycle);
+    return enqueue_cycle(h, first_cycle, two_pass);
   if (!h->cycle_graph[gi])
     {
       const int64_t before = h->launches;
       cudaGraph_t graph = nullptr;
       PFC_CUDA(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-      const int rc = enqueue_cycle(h, first_cycle);
+      const int rc = enqueue_cycle(h, first_cycle, two_pass);
       cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
       if (rc != PFC_OK)
         {
@@ -263,12 +301,20 @@ static int gmres_solve(pfc_handle *h, int64_t *iters, double *final_res)
   PFC_CUDA(h, cudaMemcpyAsync(h->d_ctl.p, h->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, s));
   PFC_CUDA(h, cudaMemsetAsync(h->d_x.p, 0, h->d_x.n * sizeof(double), s));
   PFC_CUDA(h, cudaStreamSynchronize(s)); // h_ctl is reused as the read-back buffer
-  bool first = true;
+  bool first = true, two_pass = h->prm.orthogonalization == PFC_ORTHO_CGS2;
   for (;;)
     {
-      PFC_TRY(run_cycle(h, first));
+      PFC_TRY(run_cycle(h, first, two_pass));
       first = false;
       PFC_CUDA(h, cudaStreamSynchronize(s));
+      if (h->h_ctl->state == 3)
+        { // Kelley test tripped: go on with two Gram-Schmidt passes per iteration (sticky)
+          two_pass = true;
+          h->h_ctl->state = 0;
+          PFC_CUDA(h, cudaMemcpyAsync(h->d_ctl.p, h->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, s));
+          PFC_CUDA(h, cudaStreamSynchronize(s));
+          continue;
+        }
       if (h->h_ctl->state != 0)
         break;
     }
@@ -487,10 +533,10 @@ extern "C" int pfc_time_operator(pfc_handle *h, int32_t reps, double *ms_mean, d
   const Plan &P = h->plan;
   double *vx = h->d_V.p, *vy = h->d_V.p + h->stride;
   for (int i = 0; i < 3; ++i)
-    PFC_TRY(launch_spmv(h, vx, vy, nullptr));
+    PFC_TRY(apply_operator(h, vx, vy, nullptr));
   PFC_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
   for (int i = 0; i < reps; ++i)
-    PFC_TRY(launch_spmv(h, vx, vy, nullptr));
+    PFC_TRY(apply_operator(h, vx, vy, nullptr));
   PFC_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
   PFC_CUDA(h, cudaStreamSynchronize(h->stream));
   float ms;
@@ -499,7 +545,9 @@ extern "C" int pfc_time_operator(pfc_handle *h, int32_t reps, double *ms_mean, d
   if (bytes_per_launch)
     // layout-true algorithmic bytes: per stored entry col 4 + B,C,M,K 32; per row x read 24 + y write 24;
     // slice pointers 8 per 32 rows
-    *bytes_per_launch = 36.0 * (double)P.n_ent + 48.0 * (double)P.Np + 8.0 * (double)P.n_slices;
+    *bytes_per_launch = h->prm.operator_kind == PFC_OPERATOR_MATRIX_FREE
+                          ? 64.0 * (double)P.Np + (double)P.n_cells * (16.0 * P.n_s + 16.0) // x, y, psi, chi + cell tables
+                          : 36.0 * (double)P.n_ent + 48.0 * (double)P.Np + 8.0 * (double)P.n_slices;
   return PFC_OK;
 }
 

@@ -192,3 +192,36 @@ def test_against_committed_golden(built, name, degree, n_refines):
         assert _rel(a, b) <= 1e-9, (k, _rel(a, b))
     assert max(abs(int(x) - int(y)) for x, y in zip(tot, g["all_gmres_iters"])) <= 3, (tot, g["all_gmres_iters"])
     s.close()
+
+
+@pytest.mark.parametrize("degree,n_refines,theta", [(1, 4, 1.0), (1, 6, 0.5), (2, 3, 1.0), (2, 5, 0.5), (1, 1, 1.0), (2, 1, 1.0)])
+def test_matrix_free_operator_matches_csr(built, degree, n_refines, theta):
+    """north_star item 2: ||J_mf x - J_csr x|| / ||J_csr x|| <= 1e-13 on random x."""
+    om, st, s, Psi = _setup(built, degree, n_refines, theta, operator_kind=1)
+    Psi1 = Psi + 1e-2 * np.random.default_rng(7).standard_normal(Psi.size)
+    om.distribute(Psi1)
+    s.set_state(Psi1, Psi)
+    s.assemble()
+    ovals, orhs = om.assemble(Psi1, Psi, DT, theta, EPS)
+    rhs = s.get_rhs()
+    assert np.max(np.abs(rhs - orhs)) <= 1e-13 * np.max(np.abs(orhs))
+    x = np.random.default_rng(3).standard_normal(3 * om.N)
+    y, ref = s.apply_operator(x), om.spmv(ovals, x)
+    assert np.linalg.norm(y - ref) <= 1e-13 * np.linalg.norm(ref)
+    assert np.max(np.abs(y - ref)) <= 1e-12 * np.max(np.abs(ref))
+    s.close()
+
+
+@pytest.mark.parametrize("degree,n_refines,n_steps", [(1, 6, 2), (2, 4, 2)])
+def test_matrix_free_step_parity(built, degree, n_refines, n_steps):
+    om, st, s, Psi = _setup(built, degree, n_refines, operator_kind=1)
+    s.set_state(Psi, Psi)
+    Pn, Pn1 = Psi.copy(), Psi.copy()
+    for step in range(n_steps):
+        g = s.step()
+        o = om.newton_step(Pn, Pn1, DT, 1.0, EPS)
+        got = s.get_state()
+        print(f"mf step {step}: gmres gpu {g['gmres_iters']} oracle {o['gmres_iters']} rel {_rel(got, Pn):.2e}")
+        assert g["status"] == 0 and g["n_assemblies"] == o["n_assemblies"]
+        assert _rel(got[:om.N], Pn[:om.N]) <= 1e-9 and _rel(got, Pn) <= 1e-9
+    s.close()
