@@ -38,7 +38,13 @@ enum
   PFC_ERR_STATE = 8           /* call order (e.g. pfc_step before pfc_setup) */
 };
 
-enum { PFC_OPERATOR_ASSEMBLED = 0, PFC_OPERATOR_MATRIX_FREE = 1 };
+enum
+{
+  PFC_OPERATOR_ASSEMBLED = 0,
+  PFC_OPERATOR_MATRIX_FREE = 1,         /* lattice kernels (sum-factorised, no index tables) when the mesh is the
+                                           uniform periodic tensor lattice the reference always builds, else general */
+  PFC_OPERATOR_MATRIX_FREE_GENERAL = 2  /* colour-ordered table-driven cell kernel on any supported mesh */
+};
 enum
 {
   PFC_ORTHO_CGS = 0,   /* classical Gram-Schmidt, one fused pass, Kelley re-orthogonalisation test */
@@ -217,6 +223,21 @@ typedef struct pfc_plan_view
   const int64_t *recv_ptr;
 } pfc_plan_view;
 int  pfc_plan_build(const pfc_mesh *mesh, int32_t degree, pfc_plan **out, char *err, int32_t err_len);
+/* flags: 1 = look for the uniform periodic tensor lattice behind the arrays (what make_grid, mpi.cpp:115-146,
+ * always produces) and number the owned free nodes lexicographically, as pfc_setup does for
+ * PFC_OPERATOR_MATRIX_FREE; 2 = additionally skip the SELL pattern and per-cell tables */
+int  pfc_plan_build_ex(const pfc_mesh *mesh, int32_t degree, int32_t flags, pfc_plan **out, char *err, int32_t err_len);
+typedef struct pfc_lattice_view
+{
+  int32_t active, degree;            /* active = 0: `why` says what ruled the lattice out */
+  int32_t ncx, ncy;                  /* frame: the cells touching an owned free node */
+  int32_t ex0, ey0, w, h;            /* owned free nodes: frame rectangle [ex0, ex0+w) x [ey0, ey0+h) */
+  int32_t fw, fh;                    /* frame nodes per direction: degree * ncx + 1, degree * ncy + 1 */
+  double  hx, hy;
+  const int32_t *lut;                /* [fh][fw] internal id of the resolved node at a frame position */
+  char why[128];
+} pfc_lattice_view;
+void pfc_plan_get_lattice(const pfc_plan *p, pfc_lattice_view *view);
 void pfc_plan_get_view(const pfc_plan *p, pfc_plan_view *view);
 /* monolithic CSR the reference would build (mpi.cpp:220-244) + where each entry lives:
  * block_of 0 B, 1 C, 2 D, 3 K, 4 M; pos_of = entry position in the SELL arrays (single rank) */

@@ -25,7 +25,8 @@ PFC_ERR_NONFINITE = 5
 PFC_WARN_NEWTON_MAX_ITERS = 6
 PFC_ERR_UNSUPPORTED = 7
 PFC_ERR_STATE = 8
-OPERATOR_ASSEMBLED, OPERATOR_MATRIX_FREE = 0, 1
+OPERATOR_ASSEMBLED, OPERATOR_MATRIX_FREE, OPERATOR_MATRIX_FREE_GENERAL = 0, 1, 2
+PLAN_LATTICE, PLAN_SKIP_TABLES = 1, 2
 ORTHO_CGS, ORTHO_CGS2, ORTHO_MGS = 0, 1, 2
 PRECOND_NONE, PRECOND_BLOCK_SCHUR = 0, 1
 MAX_NEWTON_RECORD = 256
@@ -93,6 +94,11 @@ class PlanView(C.Structure):
                 ("recv_ptr", _i64p)]
 
 
+class LatticeView(C.Structure):
+    _fields_ = [(k, C.c_int32) for k in ("active", "degree", "ncx", "ncy", "ex0", "ey0", "w", "h", "fw", "fh")] + \
+               [("hx", C.c_double), ("hy", C.c_double), ("lut", _i32p), ("why", C.c_char * 128)]
+
+
 # every symbol include/pfc_b200.h declares (tests check the library exports all of them)
 EXPORTED_SYMBOLS = [
     "pfc_default_params", "pfc_create", "pfc_destroy", "pfc_last_error", "pfc_version", "pfc_setup",
@@ -102,7 +108,7 @@ EXPORTED_SYMBOLS = [
     "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_standin_create",
     "pfc_standin_create_ex", "pfc_standin_destroy",
     "pfc_standin_mesh", "pfc_standin_n_nodes", "pfc_standin_support_points",
-    "pfc_standin_hexagonal_lattice", "pfc_plan_build", "pfc_plan_get_view", "pfc_plan_monolithic",
+    "pfc_standin_hexagonal_lattice", "pfc_plan_build", "pfc_plan_build_ex", "pfc_plan_get_lattice", "pfc_plan_get_view", "pfc_plan_monolithic",
     "pfc_plan_destroy",
 ]
 
@@ -182,6 +188,9 @@ def lib():
     L.pfc_standin_support_points.restype = _f64p
     L.pfc_standin_hexagonal_lattice.argtypes = [hp, C.c_double, C.c_double, C.c_int32, _f64p, _f64p, _f64p]
     L.pfc_plan_build.argtypes = [C.POINTER(MeshStruct), C.c_int32, C.POINTER(hp), C.c_char_p, C.c_int32]
+    L.pfc_plan_build_ex.argtypes = [C.POINTER(MeshStruct), C.c_int32, C.c_int32, C.POINTER(hp), C.c_char_p, C.c_int32]
+    L.pfc_plan_get_lattice.argtypes = [hp, C.POINTER(LatticeView)]
+    L.pfc_plan_get_lattice.restype = None
     L.pfc_plan_get_view.argtypes = [hp, C.POINTER(PlanView)]
     L.pfc_plan_get_view.restype = None
     L.pfc_plan_monolithic.argtypes = [hp, _i64p, _i32p, C.POINTER(C.c_int8), _i32p]
@@ -253,21 +262,26 @@ class StandIn:
 class HostPlan:
     """Host-only view of what pfc_setup derives (no GPU needed)."""
 
-    def __init__(self, mesh_ptr, degree):
+    def __init__(self, mesh_ptr, degree, flags=0):
         self._h = C.c_void_p()
         err = C.create_string_buffer(512)
-        rc = lib().pfc_plan_build(mesh_ptr, degree, C.byref(self._h), err, 512)
+        rc = lib().pfc_plan_build_ex(mesh_ptr, degree, flags, C.byref(self._h), err, 512)
         if rc != PFC_OK:
             raise PfcError(rc, err.value.decode())
         v = PlanView()
         lib().pfc_plan_get_view(self._h, C.byref(v))
+        lv = LatticeView()
+        lib().pfc_plan_get_lattice(self._h, C.byref(lv))
+        self.lattice = {k: getattr(lv, k) for k, _ in LatticeView._fields_ if k not in ("lut", "why")}
+        self.lattice["why"] = lv.why.decode()
+        self.lattice["lut"] = (np.ctypeslib.as_array(lv.lut, (lv.fh, lv.fw)).copy() if lv.active else None)
         for k, _ in PlanView._fields_[:16]:
             setattr(self, k, getattr(v, k))
         arr = np.ctypeslib.as_array
         ns = self.n_s
 
         def get(ptr, shape):
-            return arr(ptr, shape) if int(np.prod(shape)) > 0 else np.zeros(shape, dtype=np.int32)
+            return arr(ptr, shape) if (int(np.prod(shape)) > 0 and bool(ptr)) else np.zeros(shape, dtype=np.int32)
 
         self.perm = get(v.perm, (self.Np,))
         self.iperm = get(v.iperm, (self.n_owned,))
@@ -276,13 +290,13 @@ class HostPlan:
         self.row_master = get(v.row_master, (self.Np,))
         self.col = get(v.col, (self.n_ent,))
         self.slice_ptr = arr(v.slice_ptr, (self.n_slices + 1,))
-        self.color_ptr = arr(v.color_ptr, (self.n_colors + 1,))
+        self.color_ptr = get(v.color_ptr, (self.n_colors + 1,))
         self.cell_src = get(v.cell_src, (self.n_cells,))
         self.cell_gather = get(v.cell_gather, (self.n_cells, ns))
         self.cell_row = get(v.cell_row, (self.n_cells, ns))
         self.cell_pos = get(v.cell_pos, (self.n_cells, ns, ns))
         self.cell_spos = get(v.cell_spos, (self.n_cells, ns))
-        self.cell_h = arr(v.cell_h, (self.n_cells, 2))
+        self.cell_h = get(v.cell_h, (self.n_cells, 2))
         self.slave_id = get(v.slave_id, (self.n_slaves,))
         self.slave_master = get(v.slave_master, (self.n_slaves,))
         self.peers = get(v.peers, (self.n_peers,))

@@ -24,7 +24,7 @@ int fail(Plan &p, int code, const std::string &msg)
 }
 } // namespace
 
-int build_plan(const pfc_mesh &m, int degree, Plan &P)
+int build_plan(const pfc_mesh &m, int degree, Plan &P, int flags)
 {
   P = Plan();
   if (degree < 1 || degree > 2)
@@ -188,22 +188,28 @@ int build_plan(const pfc_mesh &m, int degree, Plan &P)
       return fail(P, PFC_ERR_BAD_ARGUMENT, "internal: ghosts on a single rank");
   }
 
+  const int64_t n_owned = P.n_owned;
+  if (flags & PLAN_LATTICE)
+    detect_lattice(m, P, cnode, master, h_of);
+  const bool skip_tables = P.lat.active && (flags & PLAN_SKIP_TABLES);
+  P.has_tables = !skip_tables;
+
   // ---- rows of the scalar pattern (owned nodes), columns as ascending GLOBAL node ids ----------
   // adjacency: resolved owned node -> cells
-  const int64_t n_owned = P.n_owned;
+  const int64_t n_cells_tab = skip_tables ? 0 : m.n_cells, n_rows_tab = skip_tables ? 0 : n_owned;
   std::vector<int64_t> adj_ptr(n_owned + 1, 0);
-  for (int64_t k = 0; k < m.n_cells * ns; ++k)
+  for (int64_t k = 0; k < n_cells_tab * ns; ++k)
     {
       const int32_t r = master[cnode[k]];
       if (owned(r))
         adj_ptr[r - own0 + 1]++;
     }
-  for (int64_t i = 0; i < n_owned; ++i)
+  for (int64_t i = 0; i < n_rows_tab; ++i)
     adj_ptr[i + 1] += adj_ptr[i];
   std::vector<int32_t> adj(adj_ptr[n_owned]);
   {
     std::vector<int64_t> fill(adj_ptr.begin(), adj_ptr.end() - 1);
-    for (int64_t cell = 0; cell < m.n_cells; ++cell)
+    for (int64_t cell = 0; cell < n_cells_tab; ++cell)
       for (int a = 0; a < ns; ++a)
         {
           const int32_t r = master[cnode[cell * ns + a]];
@@ -217,7 +223,7 @@ int build_plan(const pfc_mesh &m, int degree, Plan &P)
   {
     const int maxrow = 4 * ns * 4; // generous: a node is shared by <= 4 cells (+ periodic images)
 #pragma omp parallel for schedule(static)
-    for (int64_t i = 0; i < n_owned; ++i)
+    for (int64_t i = 0; i < n_rows_tab; ++i)
       {
         const int64_t t = own0 + i;
         if (master[t] != t)
@@ -233,11 +239,11 @@ int build_plan(const pfc_mesh &m, int degree, Plan &P)
         std::sort(tmp.begin(), tmp.end());
         row_len[i] = (int32_t)(std::unique(tmp.begin(), tmp.end()) - tmp.begin());
       }
-    for (int64_t i = 0; i < n_owned; ++i)
+    for (int64_t i = 0; i < n_rows_tab; ++i)
       grow_ptr[i + 1] = grow_ptr[i] + row_len[i];
     gcol.resize(grow_ptr[n_owned]);
 #pragma omp parallel for schedule(static)
-    for (int64_t i = 0; i < n_owned; ++i)
+    for (int64_t i = 0; i < n_rows_tab; ++i)
       {
         const int64_t t = own0 + i;
         if (master[t] != t)
@@ -254,7 +260,7 @@ int build_plan(const pfc_mesh &m, int degree, Plan &P)
         std::copy(tmp.begin(), tmp.end(), gcol.begin() + grow_ptr[i]);
       }
   }
-  for (int64_t i = 0; i < n_owned; ++i)
+  for (int64_t i = 0; i < n_rows_tab; ++i)
     if (master[own0 + i] == own0 + i && row_len[i] == 0)
       return fail(P, PFC_ERR_BAD_ARGUMENT, "an owned free dof is not touched by any cell handed over");
 
@@ -265,12 +271,24 @@ int build_plan(const pfc_mesh &m, int degree, Plan &P)
   {
     std::vector<int32_t> idx(n_owned);
     std::iota(idx.begin(), idx.end(), 0);
-    for (int64_t w0 = 0; w0 < n_owned; w0 += kSigma)
-      {
-        const int64_t w1 = std::min<int64_t>(n_owned, w0 + kSigma);
-        std::stable_sort(idx.begin() + w0, idx.begin() + w1,
-                         [&](int32_t a, int32_t b) { return row_len[a] > row_len[b]; });
+    if (P.lat.active)
+      { // lattice numbering: owned free nodes lexicographic (y, x), then the owned slaves by global id
+        int64_t r = 0;
+        for (int32_t g : P.lat.order)
+          idx[r++] = (int32_t)(g - own0);
+        for (int64_t t = own0; t < own1; ++t)
+          if (master[t] != t)
+            idx[r++] = (int32_t)(t - own0);
+        if (r != n_owned)
+          return fail(P, PFC_ERR_BAD_ARGUMENT, "internal: lattice numbering does not cover the owned nodes");
       }
+    else
+      for (int64_t w0 = 0; w0 < n_owned; w0 += kSigma)
+        {
+          const int64_t w1 = std::min<int64_t>(n_owned, w0 + kSigma);
+          std::stable_sort(idx.begin() + w0, idx.begin() + w1,
+                           [&](int32_t a, int32_t b) { return row_len[a] > row_len[b]; });
+        }
     for (int64_t r = 0; r < n_owned; ++r)
       {
         P.perm[r] = (int32_t)(own0 + idx[r]);
@@ -293,6 +311,29 @@ int build_plan(const pfc_mesh &m, int degree, Plan &P)
       P.row_len[r] = row_len[P.perm[r] - own0];
     }
 
+  // ---- lattice: frame position -> internal id ----------------------------------------------------
+  if (P.lat.active)
+    {
+      Lattice &L = P.lat;
+      L.lut.resize(L.lut_global.size());
+      for (size_t k = 0; k < L.lut_global.size(); ++k)
+        {
+          const int32_t g = L.lut_global[k];
+          if (g < 0 || g2l[g] < 0)
+            return fail(P, PFC_ERR_BAD_ARGUMENT, "internal: lattice frame position without a local node");
+          L.lut[k] = g2l[g];
+        }
+      for (int64_t ly = 0; ly < L.h; ++ly)
+        for (int64_t lx = 0; lx < L.w; ++lx)
+          if (L.lut[(size_t)((L.ey0 + ly) * L.fw + L.ex0 + lx)] != (int32_t)(ly * L.w + lx))
+            return fail(P, PFC_ERR_BAD_ARGUMENT, "internal: lattice numbering mismatch");
+      std::vector<int32_t>().swap(L.lut_global);
+    }
+
+  P.n_slices = P.Np / kSlice;
+  P.slice_ptr.assign(P.n_slices + 1, 0);
+  if (!skip_tables)
+    {
   // ---- SELL-32 arrays ---------------------------------------------------------------------------
   P.n_slices = P.Np / kSlice;
   P.slice_ptr.assign(P.n_slices + 1, 0);
@@ -434,6 +475,7 @@ int build_plan(const pfc_mesh &m, int degree, Plan &P)
   if (bad_pos)
     return fail(P, PFC_ERR_BAD_ARGUMENT, "local entry missing from the derived pattern, or a cell whose own nodes are identified by periodicity");
 
+    }
   // ---- periodic slaves among the local nodes (constraints.distribute, mpi.cpp:485) -------------
   for (int64_t t = 0; t < N; ++t)
     if (master[t] != t && g2l[t] >= 0)
@@ -461,7 +503,7 @@ int build_plan(const pfc_mesh &m, int degree, Plan &P)
     }
 
   // ---- monolithic nnz (single rank) ------------------------------------------------------------
-  if (P.n_ranks == 1)
+  if (P.n_ranks == 1 && !skip_tables)
     {
       int64_t nnz = 0;
       for (int64_t i = 0; i < n_owned; ++i)

@@ -15,6 +15,32 @@ namespace pfc
 constexpr int kSlice = 32;      // SELL slice height = one warp
 constexpr int kSigma = 4096;    // sorting window (rows) of SELL-C-sigma
 
+// Uniform tensor lattice view of the local mesh (pfc_lattice.cpp).  The reference only ever builds one
+// hyper_rectangle refined globally (mpi.cpp:119-122,145): identical axis-aligned cells, periodic in x and y.
+// When the arrays handed to pfc_setup have that structure the matrix-free path numbers the owned free
+// nodes lexicographically and addresses everything by lattice arithmetic (no per-cell index tables).
+// Local frame: ncx x ncy cells = every cell that touches an owned free node; frame node (ex, ey),
+// 0 <= ex <= p ncx, holds the resolved (periodic master) node at that position; the owned free nodes are
+// the rectangle [ex0, ex0 + w) x [ey0, ey0 + h) with internal id (ey - ey0) w + (ex - ex0); every other
+// frame position goes through lut (ghost ids, or owned ids of periodic images).
+struct Lattice
+{
+  bool active = false;
+  int p = 0;
+  int32_t ncx = 0, ncy = 0, ex0 = 0, ey0 = 0, w = 0, h = 0, fw = 0, fh = 0;
+  double hx = 0, hy = 0;
+  std::vector<int32_t> lut;        // [fh][fw] internal id (after numbering)
+  std::vector<int32_t> lut_global; // [fh][fw] global resolved node (detection product)
+  std::vector<int32_t> order;      // [w h] global node of owned free node (ly, lx), lexicographic
+  std::string why;                 // why the lattice path is not available
+};
+
+enum
+{
+  PLAN_LATTICE = 1,      // try the lattice numbering (matrix-free path)
+  PLAN_SKIP_TABLES = 2   // with an active lattice: skip SELL pattern, colouring and per-cell tables
+};
+
 struct Plan
 {
   // sizes
@@ -64,11 +90,22 @@ struct Plan
   std::vector<int64_t> recv_ptr;        // [n_peers+1] ghost index ranges (ghosts sorted by owner)
   // monolithic view (single rank only): pattern the reference would build (mpi.cpp:232-244)
   int64_t nnz_mono = 0;
+  bool has_tables = true;               // SELL pattern + per-cell tables were built
+  Lattice lat;
   std::string error;
 };
 
 // builds the plan; returns PFC_OK or an error code with plan.error set
-int build_plan(const pfc_mesh &mesh, int degree, Plan &plan);
+int build_plan(const pfc_mesh &mesh, int degree, Plan &plan, int flags = 0);
+
+// pfc_lattice.cpp: fills plan.lat (lut_global, order, frame sizes); false + lat.why when the mesh is not a
+// uniform periodic tensor lattice with a rectangular owned region
+bool detect_lattice(const pfc_mesh &mesh, Plan &plan, const std::vector<int32_t> &cnode,
+                    const std::vector<int32_t> &master, const std::vector<double> &h_of);
+// built-in FE_Q(p) x QGauss(p+1) 1-D tables the lattice kernels are compiled with
+double lattice_shape_1d(int p, int q, int j);
+double lattice_dshape_1d(int p, int q, int j);
+double lattice_weight_1d(int p, int q);
 
 // monolithic CSR (mpi.cpp:220-244) derived from the plan (single rank): row_ptr [n_dofs+1],
 // col_idx [nnz], and for every monolithic entry where it lives: block id (0 B,1 C,2 D,3 K,4 M)

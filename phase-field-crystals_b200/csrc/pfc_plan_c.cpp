@@ -11,11 +11,39 @@ struct pfc_plan
 
 extern "C" int pfc_plan_build(const pfc_mesh *mesh, int32_t degree, pfc_plan **out, char *err, int32_t err_len)
 {
+  return pfc_plan_build_ex(mesh, degree, 0, out, err, err_len);
+}
+
+extern "C" void pfc_plan_get_lattice(const pfc_plan *p, pfc_lattice_view *v)
+{
+  if (!p || !v)
+    return;
+  const pfc::Lattice &L = p->P.lat;
+  std::memset(v, 0, sizeof(*v));
+  v->active = L.active ? 1 : 0;
+  v->degree = L.p;
+  v->ncx = L.ncx;
+  v->ncy = L.ncy;
+  v->ex0 = L.ex0;
+  v->ey0 = L.ey0;
+  v->w = L.w;
+  v->h = L.h;
+  v->fw = L.fw;
+  v->fh = L.fh;
+  v->hx = L.hx;
+  v->hy = L.hy;
+  v->lut = L.lut.data();
+  std::snprintf(v->why, sizeof(v->why), "%s", L.why.c_str());
+}
+
+extern "C" int pfc_plan_build_ex(const pfc_mesh *mesh, int32_t degree, int32_t flags, pfc_plan **out, char *err,
+                                 int32_t err_len)
+{
   if (!mesh || !out)
     return PFC_ERR_BAD_ARGUMENT;
   *out = nullptr;
   pfc_plan *p = new pfc_plan();
-  const int rc = pfc::build_plan(*mesh, degree, p->P);
+  const int rc = pfc::build_plan(*mesh, degree, p->P, flags);
   if (rc != PFC_OK)
     {
       if (err && err_len > 0)
