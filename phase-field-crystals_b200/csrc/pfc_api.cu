@@ -74,7 +74,8 @@ extern "C" int pfc_create(const pfc_params *p, pfc_handle **out)
       g_create_error = "orthogonalization must be PFC_ORTHO_CGS or PFC_ORTHO_CGS2";
       return PFC_ERR_UNSUPPORTED;
     }
-  if ((p->operator_kind != PFC_OPERATOR_ASSEMBLED && p->operator_kind != PFC_OPERATOR_MATRIX_FREE) ||
+  if ((p->operator_kind != PFC_OPERATOR_ASSEMBLED && p->operator_kind != PFC_OPERATOR_MATRIX_FREE &&
+       p->operator_kind != PFC_OPERATOR_MATRIX_FREE_GENERAL) ||
       (p->preconditioner != PFC_PRECOND_NONE && p->preconditioner != PFC_PRECOND_BLOCK_SCHUR) || p->precond_sweeps > 16)
     {
       g_create_error = "operator_kind / preconditioner not available in this build";
@@ -153,12 +154,14 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
   if (mesh->n_ranks > 1 && (!h->comm || h->comm_size != mesh->n_ranks || h->comm_rank != mesh->rank))
     return h->fail(PFC_ERR_STATE, "pfc_comm_init must precede pfc_setup for n_ranks > 1 (same rank / n_ranks)");
   Plan &P = h->plan;
-  int rc = build_plan(*mesh, h->prm.degree, P);
+  const int plan_flags = h->prm.operator_kind == PFC_OPERATOR_MATRIX_FREE ? (PLAN_LATTICE | PLAN_SKIP_TABLES) : 0;
+  int rc = build_plan(*mesh, h->prm.degree, P, plan_flags);
+  h->lat = P.lat.active;
   if (rc != PFC_OK)
     return h->fail(rc, "pfc_setup: %s", P.error.c_str());
 
   // host pattern check (mpi.cpp:232-244): bit-identical or refused
-  if (mesh->row_ptr && mesh->col_idx && P.n_ranks == 1)
+  if (mesh->row_ptr && mesh->col_idx && P.n_ranks == 1 && P.has_tables)
     {
       std::vector<int64_t> rp;
       std::vector<int32_t> ci;
@@ -251,8 +254,8 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
       }
   h->is_setup = true;
   // iterate-independent blocks M and K, once (they are re-assembled every Newton iteration
-  // upstream, mpi.cpp:435-443, with identical values)
-  rc = launch_assembly(h, true);
+  // upstream, mpi.cpp:435-443, with identical values); the lattice path stores no matrix at all
+  rc = h->lat ? lat_setup(h) : launch_assembly(h, true);
   if (rc != PFC_OK)
     {
       h->is_setup = false;
@@ -333,7 +336,7 @@ extern "C" int pfc_get_rhs(pfc_handle *h, double *rhs)
   return download_vector(h, h->d_rhs.p, rhs);
 }
 
-extern "C" int64_t pfc_get_nnz(pfc_handle *h) { return (h && h->is_setup) ? h->plan.nnz_mono : -1; }
+extern "C" int64_t pfc_get_nnz(pfc_handle *h) { return (h && h->is_setup && h->plan.has_tables) ? h->plan.nnz_mono : -1; }
 
 extern "C" int pfc_get_pattern(pfc_handle *h, int64_t *row_ptr, int32_t *col_idx)
 {
@@ -343,6 +346,8 @@ extern "C" int pfc_get_pattern(pfc_handle *h, int64_t *row_ptr, int32_t *col_idx
     return h->fail(PFC_ERR_STATE, "pfc_get_pattern before pfc_setup");
   if (h->plan.n_ranks != 1)
     return h->fail(PFC_ERR_UNSUPPORTED, "monolithic inspection is single-rank only");
+  if (!h->plan.has_tables)
+    return h->fail(PFC_ERR_UNSUPPORTED, "the lattice matrix-free path stores no sparsity pattern (use PFC_OPERATOR_ASSEMBLED)");
   std::vector<int64_t> rp;
   std::vector<int32_t> ci;
   monolithic_pattern(h->plan, rp, ci, nullptr, nullptr);
@@ -359,6 +364,8 @@ extern "C" int pfc_get_matrix_values(pfc_handle *h, double *values)
     return h->fail(PFC_ERR_STATE, "pfc_get_matrix_values before pfc_assemble");
   if (h->plan.n_ranks != 1)
     return h->fail(PFC_ERR_UNSUPPORTED, "monolithic inspection is single-rank only");
+  if (!h->plan.has_tables)
+    return h->fail(PFC_ERR_UNSUPPORTED, "the lattice matrix-free path stores no matrix (use PFC_OPERATOR_ASSEMBLED)");
   PFC_CUDA(h, cudaSetDevice(h->device));
   const Plan &P = h->plan;
   std::vector<double> B(P.n_ent), C(P.n_ent), M(P.n_ent), K(P.n_ent);

@@ -7,6 +7,7 @@
 #include <string>
 #include <vector>
 
+#include "pfc_lattice_args.h"
 #include "pfc_precond.cuh"
 #include "pfc_plan.h"
 
@@ -91,6 +92,12 @@ struct pfc_handle
   double eig_min = 0, eig_max = 0;
   bool eig_valid = false;
   int solves_since_eig = 0;
+
+  // lattice matrix-free path (pfc_lattice.cu): active when operator_kind = PFC_OPERATOR_MATRIX_FREE and the plan found
+  // the uniform periodic tensor lattice
+  bool lat = false;
+  pfc::DevBuf<int32_t> d_lut;
+  pfc::LatGeom lat_geom;
 
   int64_t launches = 0;
 

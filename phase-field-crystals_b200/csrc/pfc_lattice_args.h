@@ -1,0 +1,45 @@
+// pfc_lattice_args.h — argument blocks of the lattice kernels (pfc_lattice.cuh) and their host launcher
+// (pfc_lattice.cu).
+#pragma once
+#include <cstdint>
+
+struct pfc_handle;
+
+namespace pfc
+{
+struct Ctl;
+// ---- kernel arguments ---------------------------------------------------------------------------------
+struct LatGeom
+{
+  int32_t ncx, ncy, ex0, ey0, w, h, fw, fh;
+  const int32_t *lut;
+  int64_t Np;
+  double hx, hy;
+};
+
+enum
+{
+  LAT_J = 0, // y = J x                       (vec3 in3a = x, state in3b; out3 = y)
+  LAT_S = 1, // y0 = sB B v0 + sC C v1 + sD D v2 on scalar fields, epilogue `epi` (see bcd_kernel, pfc_precond.cuh)
+  LAT_K = 2, // out = (a add + k K s0) inv_ml  (kmv_kernel)
+  LAT_R = 3  // out3 = -R(Psi_n = in3a, Psi_n-1 = in3b), out = 1 / diag(B)   (assemble_system, mpi.cpp:388-417)
+};
+
+struct LatOp
+{
+  const double *in3a, *in3b;   // 3-component vectors (vaddr layout)
+  const double *s0, *s1, *s2;  // scalar fields [owned Np | ghosts]
+  const double *add, *dinv, *cheb, *inv_ml;
+  double *d, *out, *out2, *out3;
+  double a, k, sB, sC, sD;
+  double dt, theta, eps;
+  int epi;
+};
+
+
+// host side (pfc_lattice.cu)
+int lat_setup(pfc_handle *h);                                              // after build_plan: lut upload, inv_ml
+int lat_launch(pfc_handle *h, int mode, const LatOp &op, const Ctl *ctl);  // stream-ordered, graph-capturable
+LatOp lat_op(const pfc_handle *h);                                          // zeroed LatOp with dt, theta, eps
+double lat_bytes(const pfc_handle *h, int mode);                            // algorithmic bytes of one launch
+} // namespace pfc

@@ -1,4 +1,4 @@
-// pfc_lattice.cpp — host detection of the uniform tensor lattice behind the arrays of pfc_mesh.
+// pfc_lattice_plan.cpp — host detection of the uniform tensor lattice behind the arrays of pfc_mesh.
 //
 // The reference's mesh is always one hyper_rectangle refined globally and made periodic in x and y
 // (make_grid, mpi.cpp:115-146), FE_Q(p)^3 with QGauss(p+1) (mpi.cpp:84-86,308).  Nothing in the C ABI says

@@ -15,7 +15,7 @@ namespace pfc
 constexpr int kSlice = 32;      // SELL slice height = one warp
 constexpr int kSigma = 4096;    // sorting window (rows) of SELL-C-sigma
 
-// Uniform tensor lattice view of the local mesh (pfc_lattice.cpp).  The reference only ever builds one
+// Uniform tensor lattice view of the local mesh (pfc_lattice_plan.cpp).  The reference only ever builds one
 // hyper_rectangle refined globally (mpi.cpp:119-122,145): identical axis-aligned cells, periodic in x and y.
 // When the arrays handed to pfc_setup have that structure the matrix-free path numbers the owned free
 // nodes lexicographically and addresses everything by lattice arithmetic (no per-cell index tables).
@@ -98,7 +98,7 @@ struct Plan
 // builds the plan; returns PFC_OK or an error code with plan.error set
 int build_plan(const pfc_mesh &mesh, int degree, Plan &plan, int flags = 0);
 
-// pfc_lattice.cpp: fills plan.lat (lut_global, order, frame sizes); false + lat.why when the mesh is not a
+// pfc_lattice_plan.cpp: fills plan.lat (lut_global, order, frame sizes); false + lat.why when the mesh is not a
 // uniform periodic tensor lattice with a rectangular owned region
 bool detect_lattice(const pfc_mesh &mesh, Plan &plan, const std::vector<int32_t> &cnode,
                     const std::vector<int32_t> &master, const std::vector<double> &h_of);

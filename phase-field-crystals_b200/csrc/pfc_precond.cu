@@ -41,6 +41,54 @@ static inline int vgrid(const pfc_handle *h, int64_t n)
   return (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, (int64_t)h->n_sm * 8));
 }
 
+// K / B-C-D products: SELL kernels on the assembled blocks, or the matrix-free lattice cell kernel
+static void run_kmv(pfc_handle *h, const SellArgs &S, int nb, const double *add, double a, const double *v, double k,
+                    double *out, double *out2, const Ctl *ctl)
+{
+  if (h->lat)
+    {
+      LatOp op = lat_op(h);
+      op.s0 = v;
+      op.add = add;
+      op.a = a;
+      op.k = k;
+      op.out = out;
+      op.out2 = out2;
+      lat_launch(h, LAT_K, op, ctl);
+      h->launches--; // counted by the caller
+      return;
+    }
+  kmv_kernel<<<nb, kSpmvThreads, 0, h->stream>>>(S, add, a, v, k, h->d_inv_ml.p, out, out2, ctl);
+}
+
+template <int MODE>
+static void run_bcd(pfc_handle *h, const SellArgs &S, int nb, const double *v0, const double *v1, const double *v2,
+                    double sB, double sC, double sD, const double *add, const double *dinv, double *d,
+                    const double *cheb, double *out, const Ctl *ctl)
+{
+  if (h->lat)
+    {
+      LatOp op = lat_op(h);
+      op.in3b = h->d_psi_n.p;
+      op.s0 = v0;
+      op.s1 = v1;
+      op.s2 = v2;
+      op.sB = sB;
+      op.sC = sC;
+      op.sD = sD;
+      op.add = add;
+      op.dinv = dinv;
+      op.d = d;
+      op.cheb = cheb;
+      op.out = out;
+      op.epi = MODE;
+      lat_launch(h, LAT_S, op, ctl);
+      h->launches--; // counted by the caller
+      return;
+    }
+  bcd_kernel<MODE><<<nb, kSpmvThreads, 0, h->stream>>>(S, v0, v1, v2, sB, sC, sD, add, dinv, d, cheb, out, ctl);
+}
+
 // work vectors inside d_pw
 enum { W_M1 = 0, W_T, W_RHS, W_XA, W_XB, W_D, W_T1, W_T2, W_CHI };
 static inline double *wv(const pfc_handle *h, int k) { return h->d_pw.p + (int64_t)k * h->sstride; }
@@ -48,8 +96,11 @@ static inline double *wv(const pfc_handle *h, int k) { return h->d_pw.p + (int64
 // lumped mass: inv_ml = 1 / rowsum(M); M is iterate independent (assembled once in pfc_setup)
 int precond_after_setup(pfc_handle *h)
 {
-  rowdiag_kernel<true><<<sell_blocks(h), kSpmvThreads, 0, h->stream>>>(sell_args(h), h->d_inv_ml.p);
-  h->launches++;
+  if (!h->lat) // the lattice path knows the lumped mass in closed form (lat_setup)
+    {
+      rowdiag_kernel<true><<<sell_blocks(h), kSpmvThreads, 0, h->stream>>>(sell_args(h), h->d_inv_ml.p);
+      h->launches++;
+    }
   PFC_CUDA(h, cudaGetLastError());
   // deterministic start vector of the power iterations: zero on constrained / padding rows
   const Plan &P = h->plan;
@@ -75,11 +126,11 @@ static int apply_dinv_SL(pfc_handle *h, double *v, double *y)
   cudaStream_t s = h->stream;
   double *t1 = wv(h, W_T1), *t2 = wv(h, W_T2);
   PFC_TRY(halo_exchange_scalar(h, v));
-  kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, nullptr, 0.0, v, 1.0, h->d_inv_ml.p, t1, nullptr, nullptr);
+  run_kmv(h, S, nb, nullptr, 0.0, v, 1.0, t1, nullptr, nullptr);
   PFC_TRY(halo_exchange_scalar(h, t1));
-  kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, nullptr, 0.0, t1, 1.0, h->d_inv_ml.p, t2, nullptr, nullptr);
+  run_kmv(h, S, nb, nullptr, 0.0, t1, 1.0, t2, nullptr, nullptr);
   PFC_TRY(halo_exchange_scalar(h, t2));
-  bcd_kernel<2><<<nb, kSpmvThreads, 0, s>>>(S, v, t1, t2, 1.0, -1.0, 1.0, nullptr, h->d_dinvB.p, nullptr, nullptr, y, nullptr);
+  run_bcd<2>(h, S, nb, v, t1, t2, 1.0, -1.0, 1.0, nullptr, h->d_dinvB.p, nullptr, nullptr, y, nullptr);
   h->launches += 3;
   return PFC_OK;
 }
@@ -104,8 +155,11 @@ int precond_refresh(pfc_handle *h)
 {
   const Plan &P = h->plan;
   cudaStream_t s = h->stream;
-  rowdiag_kernel<false><<<sell_blocks(h), kSpmvThreads, 0, s>>>(sell_args(h), h->d_dinvB.p);
-  h->launches++;
+  if (!h->lat) // the lattice residual kernel already left 1 / diag(B) in d_dinvB
+    {
+      rowdiag_kernel<false><<<sell_blocks(h), kSpmvThreads, 0, s>>>(sell_args(h), h->d_dinvB.p);
+      h->launches++;
+    }
   const bool estimate = !h->eig_valid || h->solves_since_eig >= 16;
   if (estimate)
     {
@@ -178,9 +232,9 @@ int precond_apply(pfc_handle *h, const double *in, double *out, const Ctl *ctl)
 
   vec_mul_kernel<<<g, 256, 0, s>>>(m1, nullptr, 1.0, nullptr, r1, iml, Np, ctl);                     // m1 = M_L^-1 r1
   PFC_TRY(halo_exchange_scalar(h, m1));
-  kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, r2, 1.0, m1, -1.0, iml, t, nullptr, ctl);                // t = M_L^-1 (r2 - K m1)
+  run_kmv(h, S, nb, r2, 1.0, m1, -1.0, t, nullptr, ctl);                // t = M_L^-1 (r2 - K m1)
   PFC_TRY(halo_exchange_scalar(h, t));
-  bcd_kernel<0><<<nb, kSpmvThreads, 0, s>>>(S, nullptr, m1, t, 0.0, -1.0, -1.0, r0, nullptr, nullptr, nullptr, rhs, ctl);
+  run_bcd<0>(h, S, nb, nullptr, m1, t, 0.0, -1.0, -1.0, r0, nullptr, nullptr, nullptr, rhs, ctl);
   // Chebyshev on S_L psi = rhs, Jacobi scaling diag(B)^-1
   vec_mul_kernel<<<g, 256, 0, s>>>(d, xa, 1.0, h->d_cheb.p, rhs, h->d_dinvB.p, Np, ctl);            // d = x = dinv rhs / theta
   h->launches += 4;
@@ -188,19 +242,19 @@ int precond_apply(pfc_handle *h, const double *in, double *out, const Ctl *ctl)
   for (int i = 1; i < h->sweeps; ++i)
     {
       PFC_TRY(halo_exchange_scalar(h, x));
-      kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, nullptr, 0.0, x, 1.0, iml, t1, nullptr, ctl);
+      run_kmv(h, S, nb, nullptr, 0.0, x, 1.0, t1, nullptr, ctl);
       PFC_TRY(halo_exchange_scalar(h, t1));
-      kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, nullptr, 0.0, t1, 1.0, iml, t2, nullptr, ctl);
+      run_kmv(h, S, nb, nullptr, 0.0, t1, 1.0, t2, nullptr, ctl);
       PFC_TRY(halo_exchange_scalar(h, t2));
-      bcd_kernel<1><<<nb, kSpmvThreads, 0, s>>>(S, x, t1, t2, 1.0, -1.0, 1.0, rhs, h->d_dinvB.p, d, h->d_cheb.p + 2 * i, xn, ctl);
+      run_bcd<1>(h, S, nb, x, t1, t2, 1.0, -1.0, 1.0, rhs, h->d_dinvB.p, d, h->d_cheb.p + 2 * i, xn, ctl);
       std::swap(x, xn);
       h->launches += 3;
     }
   // back substitution; psi -> out[0], chi -> out[1], phi -> out[2]
   PFC_TRY(halo_exchange_scalar(h, x));
-  kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, r1, 1.0, x, -1.0, iml, chi, out + Np, ctl);              // chi = M_L^-1 (r1 - K psi)
+  run_kmv(h, S, nb, r1, 1.0, x, -1.0, chi, out + Np, ctl);              // chi = M_L^-1 (r1 - K psi)
   PFC_TRY(halo_exchange_scalar(h, chi));
-  kmv_kernel<<<nb, kSpmvThreads, 0, s>>>(S, r2, 1.0, chi, -1.0, iml, out + 2 * Np, nullptr, ctl);    // phi = M_L^-1 (r2 - K chi)
+  run_kmv(h, S, nb, r2, 1.0, chi, -1.0, out + 2 * Np, nullptr, ctl);    // phi = M_L^-1 (r2 - K chi)
   vec_mul_kernel<<<g, 256, 0, s>>>(out, nullptr, 1.0, nullptr, x, nullptr, Np, ctl);
   h->launches += 3;
   PFC_CUDA(h, cudaGetLastError());

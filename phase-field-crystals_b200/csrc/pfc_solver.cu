@@ -46,9 +46,25 @@ static void launch_asm_colors(pfc_handle *h, const AsmArgs &A)
 int precond_refresh(pfc_handle *h);                                                    // pfc_precond.cu
 int precond_apply(pfc_handle *h, const double *in, double *out, const pfc::Ctl *ctl); // pfc_precond.cu
 
+static inline bool is_general_mf(const pfc_handle *h)
+{
+  return !h->lat && (h->prm.operator_kind == PFC_OPERATOR_MATRIX_FREE || h->prm.operator_kind == PFC_OPERATOR_MATRIX_FREE_GENERAL);
+}
+
 int launch_assembly(pfc_handle *h, bool const_pass)
 {
   const Plan &P = h->plan;
+  if (h->lat)
+    { // -R by the lattice cell kernel; 1 / diag(B) for the Jacobi scaling of the preconditioner on the way
+      if (const_pass)
+        return PFC_OK;
+      LatOp op = lat_op(h);
+      op.in3a = h->d_psi_n.p;
+      op.in3b = h->d_psi_n1.p;
+      op.out3 = h->d_rhs.p;
+      op.out = h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR ? h->d_dinvB.p : nullptr;
+      return lat_launch(h, LAT_R, op, nullptr);
+    }
   AsmArgs A;
   A.cell_gather = h->d_cell_gather.p;
   A.cell_row = h->d_cell_row.p;
@@ -68,8 +84,7 @@ int launch_assembly(pfc_handle *h, bool const_pass)
   A.theta = h->prm.theta;
   A.eps = h->prm.eps;
   // matrix-free operator without preconditioner: B and C are never read
-  A.rhs_only = (!const_pass && h->prm.operator_kind == PFC_OPERATOR_MATRIX_FREE &&
-                h->prm.preconditioner == PFC_PRECOND_NONE) ? 1 : 0;
+  A.rhs_only = (!const_pass && is_general_mf(h) && h->prm.preconditioner == PFC_PRECOND_NONE) ? 1 : 0;
   cudaStream_t s = h->stream;
   if (const_pass)
     {
@@ -149,7 +164,15 @@ static int launch_mf(pfc_handle *h, const double *x, double *y, const Ctl *ctl)
 static int apply_operator(pfc_handle *h, double *x, double *y, const Ctl *ctl)
 {
   PFC_TRY(halo_exchange(h, x));
-  if (h->prm.operator_kind == PFC_OPERATOR_MATRIX_FREE)
+  if (h->lat)
+    {
+      LatOp op = lat_op(h);
+      op.in3a = x;
+      op.in3b = h->d_psi_n.p;
+      op.out3 = y;
+      return lat_launch(h, LAT_J, op, ctl);
+    }
+  if (is_general_mf(h))
     return h->plan.n_s == 4 ? launch_mf<4>(h, x, y, ctl) : launch_mf<9>(h, x, y, ctl);
   return launch_spmv(h, x, y, ctl);
 }
@@ -545,7 +568,7 @@ extern "C" int pfc_time_operator(pfc_handle *h, int32_t reps, double *ms_mean, d
   if (bytes_per_launch)
     // layout-true algorithmic bytes: per stored entry col 4 + B,C,M,K 32; per row x read 24 + y write 24;
     // slice pointers 8 per 32 rows
-    *bytes_per_launch = h->prm.operator_kind == PFC_OPERATOR_MATRIX_FREE
+    *bytes_per_launch = h->lat ? lat_bytes(h, LAT_J) : is_general_mf(h)
                           ? 64.0 * (double)P.Np + (double)P.n_cells * (16.0 * P.n_s + 16.0) // x, y, psi, chi + cell tables
                           : 36.0 * (double)P.n_ent + 48.0 * (double)P.Np + 8.0 * (double)P.n_slices;
   return PFC_OK;
@@ -572,8 +595,9 @@ extern "C" int pfc_time_assembly(pfc_handle *h, int32_t reps, double *ms_mean, d
   if (bytes_per_launch)
     // B, C zeroed + written (read-modify-write counted once each way): 2 * 2 * 8 per entry;
     // state read 48 / node, rhs write 24 / node; per cell tables (gather, row, spos, pos, h)
-    *bytes_per_launch = 32.0 * (double)P.n_ent + 72.0 * (double)P.Np +
-                        (double)P.n_cells * (4.0 * (3 * P.n_s + P.n_s * P.n_s) + 16.0);
+    *bytes_per_launch = h->lat ? lat_bytes(h, LAT_R)
+                               : 32.0 * (double)P.n_ent + 72.0 * (double)P.Np +
+                                   (double)P.n_cells * (4.0 * (3 * P.n_s + P.n_s * P.n_s) + 16.0);
   return PFC_OK;
 }
 

@@ -1,4 +1,4 @@
-"""Host detection of the uniform periodic tensor lattice (csrc/pfc_lattice.cpp) — no GPU needed.
+"""Host detection of the uniform periodic tensor lattice (csrc/pfc_lattice_plan.cpp) — no GPU needed.
 
 The lattice plan must (a) number the owned free nodes lexicographically, (b) map every frame position to
 the resolved (periodic master) node sitting there, on every rank of the partitions the bench uses, and
