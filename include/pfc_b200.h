@@ -179,6 +179,12 @@ int pfc_get_dof_permutation(pfc_handle *h, int32_t *internal_of_node);  /* [N] i
  * algorithmic bytes of one launch for the active layout */
 int pfc_time_operator(pfc_handle *h, int32_t reps, double *ms_mean, double *bytes_per_launch);
 int pfc_time_assembly(pfc_handle *h, int32_t reps, double *ms_mean, double *bytes_per_launch);
+/* block-Schur preconditioner legs on resident data: ms[0] one full application P^-1 v, ms[1] one K product
+ * (kmv), ms[2] one Schur-row product (Chebyshev step); bytes[] = algorithmic bytes of ms[1], ms[2] launches */
+int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms3, double *bytes2);
+/* consistency of redundant kernel forms on a deterministic pseudo-random field (lattice path: K product as node
+ * stencil vs cell quadrature); max_rel = max |a - b| / max |a|.  0 when the handle has no redundant form. [collective] */
+int pfc_selfcheck(pfc_handle *h, double *max_rel);
 /* the two Gram-Schmidt kernels at Krylov dimension dim (1..restart): multi-dot (reads dim+1
  * vectors) and multi-axpy with norm (reads dim+1, writes 1) */
 int pfc_time_krylov(pfc_handle *h, int32_t dim, int32_t reps, double *ms_dot, double *bytes_dot,

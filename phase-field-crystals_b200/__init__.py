@@ -105,7 +105,7 @@ EXPORTED_SYMBOLS = [
     "pfc_nccl_unique_id", "pfc_comm_init", "pfc_set_state", "pfc_get_state", "pfc_assemble",
     "pfc_residual_norm", "pfc_solve_update", "pfc_step", "pfc_run", "pfc_get_rhs", "pfc_get_nnz",
     "pfc_get_pattern", "pfc_get_matrix_values", "pfc_apply_operator", "pfc_get_dof_permutation",
-    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_standin_create",
+    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_standin_create",
     "pfc_standin_create_ex", "pfc_standin_destroy",
     "pfc_standin_mesh", "pfc_standin_n_nodes", "pfc_standin_support_points",
     "pfc_standin_hexagonal_lattice", "pfc_plan_build", "pfc_plan_build_ex", "pfc_plan_get_lattice", "pfc_plan_get_view", "pfc_plan_monolithic",
@@ -173,6 +173,8 @@ def lib():
     L.pfc_get_dof_permutation.argtypes = [hp, _i32p]
     L.pfc_time_operator.argtypes = [hp, C.c_int32, _f64p, _f64p]
     L.pfc_time_assembly.argtypes = [hp, C.c_int32, _f64p, _f64p]
+    L.pfc_time_precond.argtypes = [hp, C.c_int32, _f64p, _f64p]
+    L.pfc_selfcheck.argtypes = [hp, _f64p]
     L.pfc_standin_create.argtypes = [C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double,
                                      C.c_int32, C.c_int32, C.POINTER(hp)]
     L.pfc_standin_create_ex.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_double,
@@ -424,6 +426,16 @@ class Solver:
         a, b, c, d = C.c_double(), C.c_double(), C.c_double(), C.c_double()
         self._check(lib().pfc_time_krylov(self._h, dim, reps, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
         return {"ms_dot": a.value, "bytes_dot": b.value, "ms_axpy": c.value, "bytes_axpy": d.value}
+
+    def selfcheck(self):
+        v = C.c_double()
+        self._check(lib().pfc_selfcheck(self._h, C.byref(v)))
+        return v.value
+
+    def time_precond(self, reps=10):
+        ms, by = (C.c_double * 3)(), (C.c_double * 2)()
+        self._check(lib().pfc_time_precond(self._h, reps, ms, by))
+        return {"ms_apply": ms[0], "ms_kmv": ms[1], "ms_schur_row": ms[2], "bytes_kmv": by[0], "bytes_schur_row": by[1]}
 
     def time_assembly(self, reps=5):
         ms, by = C.c_double(), C.c_double()

@@ -96,6 +96,7 @@ struct pfc_handle
   // lattice matrix-free path (pfc_lattice.cu): active when operator_kind = PFC_OPERATOR_MATRIX_FREE and the plan found
   // the uniform periodic tensor lattice
   bool lat = false;
+  bool lat_k_by_cells = false; // K product by the cell-quadrature kernel instead of the node stencil (self-check)
   pfc::DevBuf<int32_t> d_lut;
   pfc::LatGeom lat_geom;
 

@@ -1,5 +1,9 @@
 // pfc_lattice.cu — host launcher of the lattice kernels (pfc_lattice.cuh).
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "pfc_handle.h"
 #include "pfc_lattice.cuh"
@@ -43,6 +47,33 @@ LatOp lat_op(const pfc_handle *h)
 int lat_launch(pfc_handle *h, int mode, const LatOp &op, const Ctl *ctl)
 {
   const bool q1 = h->plan.degree == 1;
+  if (mode == LAT_K && !h->lat_k_by_cells)
+    { // node-stencil form of the K product
+      static const int variant = getenv("PFC_KS_VARIANT") ? atoi(getenv("PFC_KS_VARIANT")) : 0;
+      const LatGeom &G = h->lat_geom;
+#define PFC_KS(KX, KY)                                                                   \
+  {                                                                                      \
+    const dim3 grid((G.w + KX - 1) / KX, (G.h + KY - 1) / KY);                           \
+    if (q1)                                                                              \
+      lat_kstencil_kernel<1, KX, KY><<<grid, KX, 0, h->stream>>>(G, op, ctl);            \
+    else                                                                                 \
+      lat_kstencil_kernel<2, KX, KY><<<grid, KX, 0, h->stream>>>(G, op, ctl);            \
+  }
+      switch (variant)
+        {
+        case 1: PFC_KS(128, 2) break;
+        case 2: PFC_KS(128, 8) break;
+        case 3: PFC_KS(128, 16) break;
+        case 4: PFC_KS(64, 4) break;
+        case 5: PFC_KS(256, 4) break;
+        case 6: PFC_KS(64, 8) break;
+        case 7: PFC_KS(256, 1) break;
+        default: PFC_KS(128, 4) break;
+        }
+#undef PFC_KS
+      h->launches++;
+      return PFC_OK;
+    }
   switch (mode)
     {
     case LAT_J: return q1 ? launch_mode<1, LAT_J>(h, op, ctl) : launch_mode<2, LAT_J>(h, op, ctl);
@@ -66,6 +97,65 @@ double lat_bytes(const pfc_handle *h, int mode)
     }
 }
 
+} // namespace pfc
+
+extern "C" int pfc_selfcheck(pfc_handle *h, double *max_rel)
+{
+  using namespace pfc;
+  if (!h || !max_rel)
+    return PFC_ERR_BAD_ARGUMENT;
+  *max_rel = 0.0;
+  if (!h->is_setup)
+    return h->fail(PFC_ERR_STATE, "pfc_selfcheck before pfc_setup");
+  if (!h->lat)
+    return PFC_OK;
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  const Plan &P = h->plan;
+  const int64_t n = P.Np + P.n_ghost;
+  if (h->stride < n)
+    return h->fail(PFC_ERR_STATE, "pfc_selfcheck: work space too small");
+  double *x = h->d_V.p, *ya = h->d_V.p + h->stride, *yb = h->d_V.p + 2 * h->stride;
+  std::vector<double> hx((size_t)n, 0.0), a((size_t)P.Np), b((size_t)P.Np);
+  for (int64_t r = 0; r < n; ++r)
+    { // value tied to the global node so that ghosts agree with their owners without an exchange
+      const int64_t g = r < P.Np ? P.perm[r] : P.ghost_global[r - P.Np];
+      if (g >= 0)
+        hx[r] = 0.5 + (double)(((uint64_t)g * 0x9E3779B97F4A7C15ull >> 40) & 0xFFFF) / 65536.0;
+    }
+  cudaStream_t s = h->stream;
+  PFC_CUDA(h, cudaMemcpyAsync(x, hx.data(), n * sizeof(double), cudaMemcpyHostToDevice, s));
+  PFC_CUDA(h, cudaMemsetAsync(ya, 0, 2 * h->stride * sizeof(double), s));
+  LatOp op = lat_op(h);
+  op.s0 = x;
+  op.k = 1.0;
+  for (int pass = 0; pass < 2; ++pass)
+    {
+      h->lat_k_by_cells = pass == 1;
+      op.out = pass == 0 ? ya : yb;
+      const int rc = lat_launch(h, LAT_K, op, nullptr);
+      h->lat_k_by_cells = false;
+      if (rc != PFC_OK)
+        return rc;
+    }
+  PFC_CUDA(h, cudaGetLastError());
+  PFC_CUDA(h, cudaMemcpyAsync(a.data(), ya, P.Np * sizeof(double), cudaMemcpyDeviceToHost, s));
+  PFC_CUDA(h, cudaMemcpyAsync(b.data(), yb, P.Np * sizeof(double), cudaMemcpyDeviceToHost, s));
+  PFC_CUDA(h, cudaStreamSynchronize(s));
+  double dmax = 0, amax = 0;
+  for (int64_t r = 0; r < P.Np; ++r)
+    {
+      dmax = std::max(dmax, std::fabs(a[r] - b[r]));
+      amax = std::max(amax, std::fabs(b[r]));
+    }
+  // leave the Krylov work space as pfc_setup left it
+  PFC_CUDA(h, cudaMemsetAsync(x, 0, 3 * h->stride * sizeof(double), s));
+  PFC_CUDA(h, cudaStreamSynchronize(s));
+  *max_rel = amax > 0 ? dmax / amax : (dmax > 0 ? 1.0 : 0.0);
+  return PFC_OK;
+}
+
+namespace pfc
+{
 int lat_setup(pfc_handle *h)
 {
   const Lattice &L = h->plan.lat;

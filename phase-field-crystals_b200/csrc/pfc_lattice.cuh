@@ -200,50 +200,69 @@ static __global__ void __launch_bounds__(CX *CY) lat_kernel(LatGeom L, LatOp O, 
   const int nx0 = P * (ax0 - 1), ny0 = P * (ay0 - 1);                 // frame position of tile node (0, 0)
   const int64_t Np = L.Np;
 
-  // ---- stage the tile's nodal values ----
-  for (int idx = tid; idx < TN; idx += NT)
-    {
-      const int i = idx % TNX, j = idx / TNX;
-      const int ex = nx0 + i, ey = ny0 + j;
-      double f[NF];
+  // ---- stage the tile's nodal values: all node ids first, then all loads in flight, then the stores ----
+  {
+    constexpr int ITER = (TN + NT - 1) / NT;
+    int32_t uid[ITER];
 #pragma unroll
-      for (int k = 0; k < NF; ++k)
-        f[k] = 0;
-      if (ex >= 0 && ex < L.fw && ey >= 0 && ey < L.fh)
-        {
-          const int32_t u = lat_id(L, ex, ey);
-          if constexpr (MODE == LAT_J)
-            {
-              f[0] = O.in3a[vaddr(u, 0, Np)];
-              f[1] = O.in3a[vaddr(u, 1, Np)];
-              f[2] = O.in3a[vaddr(u, 2, Np)];
-              f[3] = O.in3b[vaddr(u, 0, Np)];
-              f[4] = O.in3b[vaddr(u, 1, Np)];
-            }
-          else if constexpr (MODE == LAT_S)
-            {
-              f[0] = O.sB != 0.0 ? O.s0[u] : 0.0;
-              f[1] = O.s1[u];
-              f[2] = O.s2[u];
-              f[3] = O.in3b[vaddr(u, 0, Np)];
-              f[4] = O.in3b[vaddr(u, 1, Np)];
-            }
-          else if constexpr (MODE == LAT_K)
-            f[0] = O.s0[u];
-          else
-            {
+    for (int it = 0; it < ITER; ++it)
+      {
+        const int idx = tid + it * NT;
+        const int i = idx % TNX, j = idx / TNX;
+        const int ex = nx0 + i, ey = ny0 + j;
+        uid[it] = (idx < TN && ex >= 0 && ex < L.fw && ey >= 0 && ey < L.fh) ? lat_id(L, ex, ey) : -1;
+      }
+    double f[ITER][NF];
 #pragma unroll
-              for (int c = 0; c < 3; ++c)
-                {
-                  f[c] = O.in3a[vaddr(u, c, Np)];
-                  f[3 + c] = O.in3b[vaddr(u, c, Np)];
-                }
-            }
-        }
+    for (int it = 0; it < ITER; ++it)
+      {
+        const int32_t u = uid[it];
 #pragma unroll
-      for (int k = 0; k < NF; ++k)
-        s_in[k * TN + idx] = f[k];
-    }
+        for (int k = 0; k < NF; ++k)
+          f[it][k] = 0;
+        if (u >= 0)
+          {
+            if constexpr (MODE == LAT_J)
+              {
+                f[it][0] = O.in3a[vaddr(u, 0, Np)];
+                f[it][1] = O.in3a[vaddr(u, 1, Np)];
+                f[it][2] = O.in3a[vaddr(u, 2, Np)];
+                f[it][3] = O.in3b[vaddr(u, 0, Np)];
+                f[it][4] = O.in3b[vaddr(u, 1, Np)];
+              }
+            else if constexpr (MODE == LAT_S)
+              {
+                f[it][0] = O.sB != 0.0 ? O.s0[u] : 0.0;
+                f[it][1] = O.s1[u];
+                f[it][2] = O.s2[u];
+                f[it][3] = O.in3b[vaddr(u, 0, Np)];
+                f[it][4] = O.in3b[vaddr(u, 1, Np)];
+              }
+            else if constexpr (MODE == LAT_K)
+              f[it][0] = O.s0[u];
+            else
+              {
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+                  {
+                    f[it][c] = O.in3a[vaddr(u, c, Np)];
+                    f[it][3 + c] = O.in3b[vaddr(u, c, Np)];
+                  }
+              }
+          }
+      }
+#pragma unroll
+    for (int it = 0; it < ITER; ++it)
+      {
+        const int idx = tid + it * NT;
+        if (idx < TN)
+          {
+#pragma unroll
+            for (int k = 0; k < NF; ++k)
+              s_in[k * TN + idx] = f[it][k];
+          }
+      }
+  }
   __syncthreads();
 
   // ---- one cell per thread ----
@@ -575,6 +594,119 @@ static __global__ void __launch_bounds__(CX *CY) lat_kernel(LatGeom L, LatOp O, 
           if (O.out)
             O.out[r] = val[3] != 0.0 ? 1.0 / val[3] : 1.0;
         }
+    }
+}
+
+// ---- K product as a node stencil -----------------------------------------------------------------------
+// K = Kx (x) My + Mx (x) Ky with the assembled 1-D rows of FE_Q(p) on a uniform periodic line (exactly what the
+// cell quadrature produces, QGauss(p+1) integrates these polynomials exactly).  Row of a vertex node: offsets
+// -p..p; of a Q2 mid node: -1..1.  Unit-length rows; M scales with h, K with 1/h.
+template <int P>
+struct Row1;
+template <>
+struct Row1<1>
+{
+  static __host__ __device__ constexpr double M(int, int d) { return d == 0 ? 4.0 / 6.0 : 1.0 / 6.0; }
+  static __host__ __device__ constexpr double K(int, int d) { return d == 0 ? 2.0 : -1.0; }
+};
+template <>
+struct Row1<2>
+{
+  static __host__ __device__ constexpr double M(int mid, int d)
+  {
+    return mid ? (d == 0 ? 16.0 / 30.0 : ((d == 1 || d == -1) ? 2.0 / 30.0 : 0.0))
+               : (d == 0 ? 8.0 / 30.0 : ((d == 1 || d == -1) ? 2.0 / 30.0 : -1.0 / 30.0));
+  }
+  static __host__ __device__ constexpr double K(int mid, int d)
+  {
+    return mid ? (d == 0 ? 16.0 / 3.0 : ((d == 1 || d == -1) ? -8.0 / 3.0 : 0.0))
+               : (d == 0 ? 14.0 / 3.0 : ((d == 1 || d == -1) ? -8.0 / 3.0 : 1.0 / 3.0));
+  }
+};
+
+
+// out = (a add + k K s0) inv_ml on the owned free nodes; one thread = one column x kKsY rows: the 1-D x sums of
+// 2 p + kKsY rows are formed once and combined per output row.  Interior threads address by arithmetic,
+// threads whose support leaves the owned rectangle go through the frame lookup.
+template <int P, int kKsX, int kKsY> // threads along x, rows per thread
+static __global__ void __launch_bounds__(kKsX) lat_kstencil_kernel(LatGeom L, LatOp O, const Ctl *ctl)
+{
+  if (ctl && ctl->state != 0)
+    return;
+  constexpr int R = kKsY + 2 * P;
+  const int lx = blockIdx.x * kKsX + threadIdx.x, ly0 = blockIdx.y * kKsY;
+  if (lx >= L.w)
+    return;
+  const double *__restrict__ v = O.s0;
+  const int midx = (P == 2) ? ((L.ex0 + lx) & 1) : 0;
+  double kx[2 * P + 1], mx[2 * P + 1];
+  sfor<2 * P + 1>([&](auto DD) {
+    PFC_IC(dd, DD);
+    kx[dd] = (midx ? Row1<P>::K(1, dd - P) : Row1<P>::K(0, dd - P)) / L.hx;
+    mx[dd] = (midx ? Row1<P>::M(1, dd - P) : Row1<P>::M(0, dd - P)) * L.hx;
+  });
+  double rK[R], rM[R];
+  const bool interior = lx - P >= 0 && lx + P < L.w && ly0 - P >= 0 && ly0 + kKsY - 1 + P < L.h;
+  if (interior)
+    {
+      const double *p0 = v + (int64_t)(ly0 - P) * L.w + lx;
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        {
+          double sk = 0, sm = 0;
+#pragma unroll
+          for (int dd = 0; dd <= 2 * P; ++dd)
+            {
+              const double val = __ldg(p0 + (int64_t)r * L.w + (dd - P));
+              sk = fma(kx[dd], val, sk);
+              sm = fma(mx[dd], val, sm);
+            }
+          rK[r] = sk;
+          rM[r] = sm;
+        }
+    }
+  else
+    {
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        {
+          const int ey = min(max(L.ey0 + ly0 - P + r, 0), L.fh - 1);
+          double sk = 0, sm = 0;
+#pragma unroll
+          for (int dd = 0; dd <= 2 * P; ++dd)
+            {
+              const int ex = min(max(L.ex0 + lx + dd - P, 0), L.fw - 1);
+              const double val = v[lat_id(L, ex, ey)];
+              sk = fma(kx[dd], val, sk);
+              sm = fma(mx[dd], val, sm);
+            }
+          rK[r] = sk;
+          rM[r] = sm;
+        }
+    }
+#pragma unroll
+  for (int j = 0; j < kKsY; ++j)
+    {
+      const int ly = ly0 + j;
+      if (ly >= L.h)
+        break;
+      const int midy = (P == 2) ? ((L.ey0 + ly) & 1) : 0;
+      double s = 0;
+      sfor<2 * P + 1>([&](auto DD) {
+        PFC_IC(dd, DD);
+        const double my = (midy ? Row1<P>::M(1, dd - P) : Row1<P>::M(0, dd - P)) * L.hy;
+        const double ky = (midy ? Row1<P>::K(1, dd - P) : Row1<P>::K(0, dd - P)) / L.hy;
+        s = fma(my, rK[j + dd], s);
+        s = fma(ky, rM[j + dd], s);
+      });
+      const int64_t r = (int64_t)ly * L.w + lx;
+      double res = O.k * s;
+      if (O.add)
+        res += O.a * O.add[r];
+      res *= O.inv_ml[r];
+      O.out[r] = res;
+      if (O.out2)
+        O.out2[r] = res;
     }
 }
 

@@ -260,3 +260,65 @@ int precond_apply(pfc_handle *h, const double *in, double *out, const Ctl *ctl)
   PFC_CUDA(h, cudaGetLastError());
   return PFC_OK;
 }
+
+// bench.py roofline legs of the preconditioner (include/pfc_b200.h)
+extern "C" int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms3, double *bytes2)
+{
+  if (!h || reps < 1 || !ms3)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->assembled || h->prm.preconditioner != PFC_PRECOND_BLOCK_SCHUR)
+    return h->fail(PFC_ERR_STATE, "pfc_time_precond needs pfc_assemble and PFC_PRECOND_BLOCK_SCHUR");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  PFC_TRY(precond_refresh(h));
+  const Plan &P = h->plan;
+  const SellArgs S = sell_args(h);
+  const int nb = sell_blocks(h);
+  cudaStream_t s = h->stream;
+  double *in = h->d_V.p, *t1 = wv(h, W_T1), *t2 = wv(h, W_T2), *x = wv(h, W_XA), *xn = wv(h, W_XB);
+  // each leg: `reps` launches captured in one CUDA graph (the solver runs its cycle as a graph too), so the
+  // number is device time per launch, not host launch rate
+  float ms;
+  for (int leg = 0; leg < 3; ++leg)
+    {
+      cudaGraph_t graph = nullptr;
+      cudaGraphExec_t exec = nullptr;
+      const int64_t before = h->launches;
+      PFC_CUDA(h, cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+      int rc = PFC_OK;
+      for (int i = 0; i < reps && rc == PFC_OK; ++i)
+        {
+          if (leg == 0)
+            rc = precond_apply(h, in, h->d_z.p, nullptr);
+          else if (leg == 1)
+            run_kmv(h, S, nb, nullptr, 0.0, x, 1.0, t1, nullptr, nullptr);
+          else
+            run_bcd<1>(h, S, nb, x, t1, t2, 1.0, -1.0, 1.0, wv(h, W_RHS), h->d_dinvB.p, wv(h, W_D), h->d_cheb.p + 2, xn, nullptr);
+        }
+      cudaError_t e = cudaStreamEndCapture(s, &graph);
+      h->launches = before;
+      if (rc != PFC_OK)
+        {
+          if (graph)
+            cudaGraphDestroy(graph);
+          return rc;
+        }
+      PFC_CUDA(h, e);
+      PFC_CUDA(h, cudaGraphInstantiate(&exec, graph, 0));
+      cudaGraphDestroy(graph);
+      cudaGraphLaunch(exec, s); // warm-up
+      PFC_CUDA(h, cudaEventRecord(h->ev[0], s));
+      cudaGraphLaunch(exec, s);
+      PFC_CUDA(h, cudaEventRecord(h->ev[1], s));
+      PFC_CUDA(h, cudaStreamSynchronize(s));
+      cudaGraphExecDestroy(exec);
+      PFC_CUDA(h, cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]));
+      ms3[leg] = ms / reps;
+    }
+  PFC_CUDA(h, cudaGetLastError());
+  if (bytes2)
+    {
+      bytes2[0] = h->lat ? lat_bytes(h, LAT_K) : 12.0 * (double)P.n_ent + 32.0 * (double)P.Np;
+      bytes2[1] = h->lat ? lat_bytes(h, LAT_S) : 36.0 * (double)P.n_ent + 64.0 * (double)P.Np;
+    }
+  return PFC_OK;
+}

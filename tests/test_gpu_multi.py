@@ -15,7 +15,9 @@ def _n_gpus():
 
 
 @pytest.mark.parametrize("degree,n_refines,steps,extra", [(1, 5, 2, "{}"), (2, 4, 1, "{}"), (1, 4, 1, '{"use_cuda_graph": 0}'),
-                                                          (1, 5, 2, '{"preconditioner": 1}'), (2, 4, 1, '{"preconditioner": 1}')])
+                                                          (1, 5, 2, '{"preconditioner": 1}'), (2, 4, 1, '{"preconditioner": 1}'),
+                                                          (1, 5, 2, '{"operator_kind": 1}'), (2, 4, 2, '{"operator_kind": 1, "preconditioner": 1}'),
+                                                          (1, 5, 2, '{"operator_kind": 1, "preconditioner": 1}')])
 def test_ranks_match_oracle(built, degree, n_refines, steps, extra):
     n = _n_gpus()
     if n < 2:

@@ -251,3 +251,13 @@ def test_lattice_and_assembled_preconditioned_runs_agree(built):
         s.close()
     print("gmres iterations assembled / lattice:", res[0][1], res[1][1])
     assert _rel(res[1][0], res[0][0]) <= 1e-9
+
+
+@pytest.mark.parametrize("degree,n_refines", [(1, 1), (2, 1), (1, 5), (2, 4), (1, 8), (2, 7)])
+def test_lattice_k_stencil_matches_cell_quadrature(built, degree, n_refines):
+    """The node-stencil K product (assembled 1-D rows) and the cell-quadrature K product are the same operator."""
+    om, st, s, Psi = _setup(built, degree, n_refines, operator_kind=1, preconditioner=1)
+    err = s.selfcheck()
+    print("K stencil vs cells:", err)
+    assert 0.0 < err <= 1e-13
+    s.close()
