@@ -269,6 +269,7 @@ def main():
     ms_op, bytes_op = solver.time_operator(reps=20)
     kry = solver.time_krylov(dim=14, reps=10)
     ms_asm, bytes_asm = solver.time_assembly(reps=3)
+    comm_legs = solver.time_comm(reps=50) if world > 1 else None
     peak, peak_src = measured_peak()
     N = mesh.N
     nnz_csr = None
@@ -284,7 +285,8 @@ def main():
                                   "GMRES(28), right block-Schur preconditioner (lumped mass + Jacobi-Chebyshev), same tol 1e-10 abs on the true residual, Newton tol 1e-8"),
                        "operator": ("matrix-free, sum-factorised lattice cell kernels (no stored matrix)" if args.mf
                                     else "assembled (shared-pattern SELL-32)"),
-                       "orthogonalization": ["CGS+Kelley", "CGS2"][args.ortho], "cuda_graph": not args.no_graph,
+                       "orthogonalization": ["CGS+Kelley", "CGS2"][args.ortho],
+                       "comm": ["single rank", "NCCL", "peer-memory kernels over NVLink (CUDA IPC) + NCCL bootstrap"][solver.comm_mode()], "cuda_graph": not args.no_graph,
                        "l2": "working set (matrix + Krylov basis) exceeds the 126 MB L2; no flush needed",
                        "newton_assemblies_per_step": [s["n_assemblies"] for s in stats], "gmres_iters_per_step": its},
             "ms_wall_per_step": ms_wall / args.steps,
@@ -306,6 +308,8 @@ def main():
                                            "frac": bytes_asm / ms_asm / 1e6 / peak}},
             "clocks": clk.summary(),
         }
+        if comm_legs is not None:
+            line["comm_legs_us"] = comm_legs
         # the reference's monolithic CSR would move 12 nnz + 12 n_rows + 8 n_cols bytes for the same product
         if not args.mf:
             nnz_mono = 7 * (bytes_op - 48.0 * N) / 36.0  # approx: 7 blocks per stored scalar entry

@@ -152,6 +152,12 @@ int pfc_setup(pfc_handle *h, const pfc_mesh *mesh);
  * by rank 0 from pfc_nccl_unique_id and broadcast by the host (MPI_COMM_WORLD at mpi.cpp:79). */
 int pfc_nccl_unique_id(void *id_bytes128);
 int pfc_comm_init(pfc_handle *h, const void *id_bytes128, int rank, int n_ranks);
+/* after pfc_setup: 0 single rank, 1 NCCL send/recv + all-reduce, 2 peer-memory kernels over NVLink (CUDA IPC;
+ * chosen when every rank can map its neighbours, PFC_NO_P2P=1 forces NCCL) */
+int pfc_comm_mode(const pfc_handle *h);
+/* device time (ms) of one scalar halo exchange, one 3-component halo exchange and one all-reduce of 16 doubles,
+ * `reps` of each replayed from a CUDA graph [collective] */
+int pfc_time_comm(pfc_handle *h, int32_t reps, double *ms3);
 
 /* ---- state (mpi.cpp:278-296 writes Psi_n, Psi_n_1; output reads them mpi.cpp:597-619) ---- */
 int pfc_set_state(pfc_handle *h, const double *Psi_n, const double *Psi_n_1); /* [n_dofs] each */

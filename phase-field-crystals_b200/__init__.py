@@ -102,7 +102,7 @@ class LatticeView(C.Structure):
 # every symbol include/pfc_b200.h declares (tests check the library exports all of them)
 EXPORTED_SYMBOLS = [
     "pfc_default_params", "pfc_create", "pfc_destroy", "pfc_last_error", "pfc_version", "pfc_setup",
-    "pfc_nccl_unique_id", "pfc_comm_init", "pfc_set_state", "pfc_get_state", "pfc_assemble",
+    "pfc_nccl_unique_id", "pfc_comm_init", "pfc_comm_mode", "pfc_time_comm", "pfc_set_state", "pfc_get_state", "pfc_assemble",
     "pfc_residual_norm", "pfc_solve_update", "pfc_step", "pfc_run", "pfc_get_rhs", "pfc_get_nnz",
     "pfc_get_pattern", "pfc_get_matrix_values", "pfc_apply_operator", "pfc_get_dof_permutation",
     "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_standin_create",
@@ -157,6 +157,8 @@ def lib():
     L.pfc_setup.argtypes = [hp, C.POINTER(MeshStruct)]
     L.pfc_nccl_unique_id.argtypes = [C.c_void_p]
     L.pfc_comm_init.argtypes = [hp, C.c_void_p, C.c_int, C.c_int]
+    L.pfc_comm_mode.argtypes = [hp]
+    L.pfc_time_comm.argtypes = [hp, C.c_int32, _f64p]
     L.pfc_set_state.argtypes = [hp, _f64p, _f64p]
     L.pfc_get_state.argtypes = [hp, _f64p, _f64p]
     L.pfc_assemble.argtypes = [hp]
@@ -354,6 +356,14 @@ class Solver:
         _preload_nccl()
         buf = C.create_string_buffer(unique_id, 128)
         self._check(lib().pfc_comm_init(self._h, buf, rank, n_ranks))
+
+    def comm_mode(self):
+        return lib().pfc_comm_mode(self._h)
+
+    def time_comm(self, reps=50):
+        ms = (C.c_double * 3)()
+        self._check(lib().pfc_time_comm(self._h, reps, ms))
+        return {"us_halo_scalar": 1e3 * ms[0], "us_halo_vec3": 1e3 * ms[1], "us_allreduce16": 1e3 * ms[2]}
 
     def setup(self, mesh):
         ptr = mesh.mesh_ptr if hasattr(mesh, "mesh_ptr") else mesh

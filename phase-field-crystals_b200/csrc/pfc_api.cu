@@ -151,6 +151,7 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
     return PFC_ERR_BAD_ARGUMENT;
   PFC_CUDA(h, cudaSetDevice(h->device));
   h->is_setup = h->has_state = h->assembled = false;
+  comm_p2p_destroy(h); // peers hold mappings of the arena that is about to be replaced
   if (mesh->n_ranks > 1 && (!h->comm || h->comm_size != mesh->n_ranks || h->comm_rank != mesh->rank))
     return h->fail(PFC_ERR_STATE, "pfc_comm_init must precede pfc_setup for n_ranks > 1 (same rank / n_ranks)");
   Plan &P = h->plan;
@@ -218,8 +219,24 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
   PFC_CUDA(h, h->d_rhs.alloc(h->stride));
   PFC_CUDA(h, h->d_psi_n.alloc(h->stride));
   PFC_CUDA(h, h->d_psi_n1.alloc(h->stride));
-  PFC_CUDA(h, h->d_x.alloc(h->stride));
-  PFC_CUDA(h, h->d_V.alloc((size_t)h->stride * h->n_basis));
+  h->sstride = (P.Np + P.n_ghost + 15) / 16 * 16;
+  {
+    const size_t n3 = (size_t)h->n_basis + 3;
+    h->arena_off_scalar = (int64_t)(n3 * h->stride);
+    const bool pc = h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR;
+    PFC_CUDA(h, h->d_arena.alloc(n3 * h->stride + (pc ? 12 * (size_t)h->sstride : 0)));
+    PFC_CUDA(h, cudaMemsetAsync(h->d_arena.p, 0, h->d_arena.n * sizeof(double), s));
+    double *a = h->d_arena.p;
+    h->d_V.view(a, (size_t)h->stride * h->n_basis);
+    h->d_x.view(a + (size_t)h->stride * h->n_basis, h->stride);
+    h->d_z.view(a + (size_t)h->stride * (h->n_basis + 1), h->stride);
+    h->d_u.view(a + (size_t)h->stride * (h->n_basis + 2), h->stride);
+    if (pc)
+      {
+        h->d_pw.view(a + h->arena_off_scalar, (size_t)h->sstride * 9);
+        h->d_pv.view(a + h->arena_off_scalar + 9 * h->sstride, (size_t)h->sstride * 3);
+      }
+  }
   PFC_CUDA(h, h->d_io.alloc(P.n_dofs));
   PFC_CUDA(h, h->d_ctl.alloc(1));
   PFC_CUDA(h, h->d_small.alloc(1));
@@ -228,24 +245,24 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
   h->eig_valid = false;
   if (h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR)
     {
-      h->sstride = (P.Np + P.n_ghost + 15) / 16 * 16;
       PFC_CUDA(h, h->d_inv_ml.alloc(P.Np));
       PFC_CUDA(h, h->d_dinvB.alloc(P.Np));
-      PFC_CUDA(h, h->d_pw.alloc((size_t)h->sstride * 9));
-      PFC_CUDA(h, h->d_pv.alloc((size_t)h->sstride * 3));
-      PFC_CUDA(h, h->d_z.alloc(h->stride));
-      PFC_CUDA(h, h->d_u.alloc(h->stride));
       PFC_CUDA(h, h->d_cheb.alloc(64));
-      for (DevBuf<double> *b : {&h->d_pw, &h->d_pv, &h->d_z, &h->d_u, &h->d_cheb})
-        PFC_CUDA(h, cudaMemsetAsync(b->p, 0, b->n * sizeof(double), s));
+      PFC_CUDA(h, cudaMemsetAsync(h->d_cheb.p, 0, 64 * sizeof(double), s));
     }
   PFC_CUDA(h, cudaMemsetAsync(h->d_counter.p, 0, 4 * sizeof(unsigned int), s));
   PFC_CUDA(h, cudaMemsetAsync(h->d_ctl.p, 0, sizeof(Ctl), s));
   PFC_CUDA(h, cudaMemsetAsync(h->d_small.p, 0, sizeof(GmresSmall), s));
   for (DevBuf<double> *b : {&h->d_B, &h->d_C, &h->d_M, &h->d_K})
     PFC_CUDA(h, cudaMemsetAsync(b->p, 0, b->n * sizeof(double), s));
-  for (DevBuf<double> *b : {&h->d_rhs, &h->d_psi_n, &h->d_psi_n1, &h->d_x, &h->d_V})
+  for (DevBuf<double> *b : {&h->d_rhs, &h->d_psi_n, &h->d_psi_n1})
     PFC_CUDA(h, cudaMemsetAsync(b->p, 0, b->n * sizeof(double), s));
+  if (P.n_ranks > 1)
+    {
+      rc = comm_p2p_setup(h); // falls back to NCCL (h->p2p = false) when peer memory cannot be mapped
+      if (rc != PFC_OK)
+        return rc;
+    }
   for (auto &g : h->cycle_graph)
     if (g)
       {

@@ -4,8 +4,10 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <vector>
 
 #include "pfc_comm.h"
 #include "pfc_handle.h"
@@ -89,6 +91,67 @@ extern "C" int pfc_nccl_unique_id(void *id_bytes128)
   return PFC_OK;
 }
 
+extern "C" int pfc_time_comm(pfc_handle *h, int32_t reps, double *ms3)
+{
+  using namespace pfc;
+  if (!h || reps < 1 || !ms3)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->is_setup)
+    return h->fail(PFC_ERR_STATE, "pfc_time_comm before pfc_setup");
+  ms3[0] = ms3[1] = ms3[2] = 0;
+  if (h->comm_size <= 1)
+    return PFC_OK;
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  cudaStream_t s = h->stream;
+  const bool pc = h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR;
+  for (int leg = 0; leg < 3; ++leg)
+    {
+      if (leg == 0 && !pc)
+        continue;
+      cudaGraph_t graph = nullptr;
+      cudaGraphExec_t exec = nullptr;
+      const int64_t before = h->launches;
+      PFC_CUDA(h, cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+      comm_p2p_unknown_predecessor(h);
+      int rc = PFC_OK;
+      for (int i = 0; i < reps && rc == PFC_OK; ++i)
+        { // alternate between two vectors, as the solver does
+          if (leg == 0)
+            rc = halo_exchange_scalar(h, h->d_pw.p + (i & 1) * h->sstride);
+          else if (leg == 1)
+            rc = halo_exchange(h, h->d_V.p + (i & 1) * h->stride);
+          else
+            rc = allreduce_sum(h, h->d_small.p->dots1, 16);
+        }
+      cudaError_t e = cudaStreamEndCapture(s, &graph);
+      h->launches = before;
+      if (rc != PFC_OK)
+        {
+          if (graph)
+            cudaGraphDestroy(graph);
+          return rc;
+        }
+      PFC_CUDA(h, e);
+      PFC_CUDA(h, cudaGraphInstantiate(&exec, graph, 0));
+      cudaGraphDestroy(graph);
+      cudaGraphLaunch(exec, s);
+      PFC_CUDA(h, cudaEventRecord(h->ev[0], s));
+      cudaGraphLaunch(exec, s);
+      PFC_CUDA(h, cudaEventRecord(h->ev[1], s));
+      PFC_CUDA(h, cudaStreamSynchronize(s));
+      comm_p2p_unknown_predecessor(h);
+      cudaGraphExecDestroy(exec);
+      float ms;
+      PFC_CUDA(h, cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]));
+      ms3[leg] = ms / reps;
+    }
+  PFC_CUDA(h, cudaMemsetAsync(h->d_small.p, 0, sizeof(GmresSmall), s));
+  PFC_CUDA(h, cudaStreamSynchronize(s));
+  return PFC_OK;
+}
+
+extern "C" int pfc_comm_mode(const pfc_handle *h) { return !h || h->comm_size <= 1 ? 0 : (h->p2p ? 2 : 1); }
+
 extern "C" int pfc_comm_init(pfc_handle *h, const void *id_bytes128, int rank, int n_ranks)
 {
   if (!h || !id_bytes128 || n_ranks < 1 || rank < 0 || rank >= n_ranks)
@@ -110,8 +173,12 @@ extern "C" int pfc_comm_init(pfc_handle *h, const void *id_bytes128, int rank, i
 
 namespace pfc
 {
+static int p2p_allreduce(pfc_handle *h, double *dev, size_t n);
+static int p2p_halo(pfc_handle *h, double *v, int nc);
+
 void comm_destroy(pfc_handle *h)
 {
+  comm_p2p_destroy(h);
   if (h->comm)
     {
       nccl().CommDestroy((ncclComm_t)h->comm);
@@ -125,6 +192,8 @@ int allreduce_sum(pfc_handle *h, double *dev, size_t n)
 {
   if (h->comm_size <= 1)
     return PFC_OK;
+  if (h->p2p)
+    return p2p_allreduce(h, dev, n);
   PFC_NCCL(h, nccl().AllReduce(dev, dev, n, ncclDouble, ncclSum, (ncclComm_t)h->comm, h->stream));
   return PFC_OK;
 }
@@ -201,6 +270,8 @@ int halo_exchange(pfc_handle *h, double *v)
   const Plan &P = h->plan;
   if (P.n_ranks <= 1)
     return PFC_OK;
+  if (h->p2p)
+    return p2p_halo(h, v, 3);
   NcclApi &n = nccl();
   ncclComm_t comm = (ncclComm_t)h->comm;
   const int64_t ns = (int64_t)P.send_rows.size();
@@ -227,6 +298,8 @@ int halo_exchange_scalar(pfc_handle *h, double *v)
   const Plan &P = h->plan;
   if (P.n_ranks <= 1)
     return PFC_OK;
+  if (h->p2p)
+    return p2p_halo(h, v, 1);
   NcclApi &n = nccl();
   ncclComm_t comm = (ncclComm_t)h->comm;
   const int64_t ns = (int64_t)P.send_rows.size();
@@ -245,6 +318,358 @@ int halo_exchange_scalar(pfc_handle *h, double *v)
         PFC_NCCL(h, n.Recv(v + P.Np + P.recv_ptr[p], (size_t)nr, ncclDouble, P.peers[p], comm, h->stream));
     }
   PFC_NCCL(h, n.GroupEnd());
+  return PFC_OK;
+}
+
+// =====================================================================================================
+// Peer-to-peer path over NVLink / NVSwitch (single node).  NCCL needs ~20 us per small operation and a
+// preconditioned GMRES iteration has ~16 of them; here
+//   * halo exchange = ONE kernel: every rank stores the values its neighbours need straight into the ghost
+//     tail of the neighbour's vector (peer-mapped with CUDA IPC), raises an epoch flag in the neighbour's
+//     memory (st.release.sys after a system fence) and waits for the neighbours' flags (ld.acquire.sys);
+//   * all-reduce of the <= 72 Gram-Schmidt coefficients = ONE single-CTA kernel: every rank stores its
+//     values into its slot on every rank, raises a flag, waits for the others and sums the slots in rank
+//     order, so all ranks hold bitwise identical results (fixed order).
+// Epochs are counted on the device (the kernels sit inside CUDA graphs that are replayed) and all ranks run
+// the same sequence of collective kernels.  Only two consecutive exchanges can overlap in time (a rank
+// cannot send exchange n+2 before it received n+1, which its neighbour sends after consuming n), so the
+// all-reduce slots are double buffered and a halo exchange on the same vector twice in a row is separated
+// by a flag-only round.
+// =====================================================================================================
+constexpr int kMaxRanksP2P = 8;
+constexpr int kArSlot = 72;
+
+struct P2PSync
+{ // one per rank, peer-visible
+  unsigned long long halo_flag[kMaxRanksP2P]; // [source rank]: halo epochs completed by that rank
+  unsigned long long ar_flag[kMaxRanksP2P];
+  double ar_slot[2][kMaxRanksP2P][kArSlot];
+  unsigned long long halo_epoch, ar_epoch; // local
+  unsigned int block_counter;
+};
+
+struct P2PState
+{
+  int R = 0, me = 0;
+  P2PSync *sync[kMaxRanksP2P] = {};   // [rank]: mapped address (own: local allocation)
+  double *arena[kMaxRanksP2P] = {};
+  int64_t Np[kMaxRanksP2P] = {}, stride[kMaxRanksP2P] = {}, sstride[kMaxRanksP2P] = {}, offB[kMaxRanksP2P] = {};
+  int64_t recv_off[kMaxRanksP2P] = {}; // [rank q]: where my values start in q's ghost tail (nodes), -1 none
+  bool mapped_arena[kMaxRanksP2P] = {}, mapped_sync[kMaxRanksP2P] = {};
+  const double *last_v = nullptr;
+};
+
+struct P2PHaloArgs
+{
+  double *dst[kMaxRanksP2P];
+  unsigned long long *flag_peer[kMaxRanksP2P];       // peer's halo_flag[me]
+  const unsigned long long *flag_mine[kMaxRanksP2P]; // my halo_flag[peer]
+  int64_t send_ptr[kMaxRanksP2P + 1];
+  int n_peers;
+};
+
+struct P2PArArgs
+{
+  P2PSync *sync[kMaxRanksP2P];
+  int R, me;
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v)
+{
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p)
+{
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+// bounded wait: a peer that never arrives must not hang the GPU (trap -> CUDA error on the host)
+__device__ __forceinline__ void wait_flag(const unsigned long long *p, unsigned long long e)
+{
+  const long long t0 = clock64();
+  while (ld_acquire_sys(p) < e)
+    if (clock64() - t0 > 20000000000ll)
+      __trap();
+}
+
+template <int NC>
+static __global__ void __launch_bounds__(256) p2p_halo_kernel(P2PHaloArgs H, const double *__restrict__ v,
+                                                               const int32_t *__restrict__ rows, int64_t Np,
+                                                               P2PSync *sl, const Ctl *ctl)
+{
+  if (ctl && ctl->state != 0)
+    return;
+  __shared__ bool s_last;
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < H.send_ptr[H.n_peers])
+    {
+      int p = 0;
+      while (k >= H.send_ptr[p + 1])
+        ++p;
+      const int64_t j = k - H.send_ptr[p];
+      const int32_t r = rows[k];
+#pragma unroll
+      for (int c = 0; c < NC; ++c)
+        H.dst[p][NC * j + c] = v[(int64_t)c * Np + r];
+    }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0)
+    s_last = atomicAdd(&sl->block_counter, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last)
+    return;
+  const unsigned long long e = sl->halo_epoch + 1;
+  if ((int)threadIdx.x < H.n_peers)
+    {
+      st_release_sys(H.flag_peer[threadIdx.x], e);
+      wait_flag(H.flag_mine[threadIdx.x], e);
+    }
+  __syncthreads();
+  if (threadIdx.x == 0)
+    {
+      sl->halo_epoch = e;
+      sl->block_counter = 0;
+    }
+}
+
+static __global__ void __launch_bounds__(128) p2p_allreduce_kernel(P2PArArgs A, double *dev, int n, P2PSync *sl,
+                                                                    const Ctl *ctl)
+{
+  if (ctl && ctl->state != 0)
+    return;
+  const unsigned long long e = sl->ar_epoch + 1;
+  const int b = (int)(e & 1), t = threadIdx.x;
+  if (t < n)
+    {
+      const double val = dev[t];
+      for (int q = 0; q < A.R; ++q)
+        A.sync[q]->ar_slot[b][A.me][t] = val;
+    }
+  __threadfence_system();
+  __syncthreads();
+  if (t < A.R && t != A.me)
+    {
+      st_release_sys(&A.sync[t]->ar_flag[A.me], e);
+      wait_flag(&sl->ar_flag[t], e);
+    }
+  __syncthreads();
+  if (t < n)
+    {
+      double s = 0;
+      for (int src = 0; src < A.R; ++src)
+        s += *(volatile const double *)&sl->ar_slot[b][src][t];
+      dev[t] = s;
+    }
+  if (t == 0)
+    sl->ar_epoch = e;
+}
+
+static int p2p_allreduce(pfc_handle *h, double *dev, size_t n)
+{
+  P2PState &S = *h->p2p_state;
+  if (n > (size_t)kArSlot)
+    return h->fail(PFC_ERR_NCCL, "p2p all-reduce of %zu values (max %d)", n, kArSlot);
+  P2PArArgs A;
+  for (int q = 0; q < kMaxRanksP2P; ++q)
+    A.sync[q] = S.sync[q];
+  A.R = S.R;
+  A.me = S.me;
+  p2p_allreduce_kernel<<<1, 128, 0, h->stream>>>(A, dev, (int)n, S.sync[S.me], nullptr);
+  h->launches++;
+  return PFC_OK;
+}
+
+static int p2p_halo(pfc_handle *h, double *v, int nc)
+{
+  const Plan &P = h->plan;
+  P2PState &S = *h->p2p_state;
+  const int64_t off = v - h->d_arena.p;
+  if (off < 0 || off >= (int64_t)h->d_arena.n)
+    return h->fail(PFC_ERR_NCCL, "p2p halo exchange of a vector outside the peer-visible arena");
+  int64_t slot;
+  if (nc == 3)
+    {
+      if (off >= h->arena_off_scalar || off % h->stride != 0)
+        return h->fail(PFC_ERR_NCCL, "p2p halo exchange: not a three-component arena vector");
+      slot = off / h->stride;
+    }
+  else
+    {
+      if (off < h->arena_off_scalar || (off - h->arena_off_scalar) % h->sstride != 0)
+        return h->fail(PFC_ERR_NCCL, "p2p halo exchange: not a scalar arena field");
+      slot = (off - h->arena_off_scalar) / h->sstride;
+    }
+  P2PHaloArgs H;
+  std::memset(&H, 0, sizeof(H));
+  H.n_peers = (int)P.peers.size();
+  for (int p = 0; p < H.n_peers; ++p)
+    {
+      const int q = P.peers[p];
+      const int64_t base = nc == 3 ? slot * S.stride[q] + 3 * S.Np[q] + 3 * std::max<int64_t>(S.recv_off[q], 0)
+                                   : S.offB[q] + slot * S.sstride[q] + S.Np[q] + std::max<int64_t>(S.recv_off[q], 0);
+      H.dst[p] = S.arena[q] + base;
+      H.flag_peer[p] = &S.sync[q]->halo_flag[S.me];
+      H.flag_mine[p] = &S.sync[S.me]->halo_flag[q];
+      H.send_ptr[p] = P.send_ptr[p];
+    }
+  H.send_ptr[H.n_peers] = P.send_ptr[H.n_peers];
+  const int64_t ns = H.send_ptr[H.n_peers];
+  const int rounds = (v == S.last_v || S.last_v == reinterpret_cast<const double *>(1)) ? 2 : 1; // same vector twice in a row: flag-only round in between
+  for (int round = 0; round < rounds; ++round)
+    {
+      const bool flag_only = rounds == 2 && round == 0;
+      P2PHaloArgs G = H;
+      if (flag_only)
+        for (int p = 0; p <= H.n_peers; ++p)
+          G.send_ptr[p] = 0;
+      const int blocks = flag_only ? 1 : (int)std::max<int64_t>(1, (ns + 255) / 256);
+      if (nc == 3)
+        p2p_halo_kernel<3><<<blocks, 256, 0, h->stream>>>(G, v, h->d_send_rows.p, P.Np, S.sync[S.me], nullptr);
+      else
+        p2p_halo_kernel<1><<<blocks, 256, 0, h->stream>>>(G, v, h->d_send_rows.p, P.Np, S.sync[S.me], nullptr);
+      h->launches++;
+    }
+  S.last_v = v;
+  return PFC_OK;
+}
+
+void comm_p2p_destroy(pfc_handle *h)
+{
+  P2PState *S = h->p2p_state;
+  if (!S)
+    return;
+  cudaSetDevice(h->device);
+  if (h->stream)
+    cudaStreamSynchronize(h->stream);
+  for (int q = 0; q < kMaxRanksP2P; ++q)
+    {
+      if (S->mapped_arena[q])
+        cudaIpcCloseMemHandle(S->arena[q]);
+      if (S->mapped_sync[q])
+        cudaIpcCloseMemHandle(S->sync[q]);
+    }
+  if (S->sync[S->me])
+    cudaFree(S->sync[S->me]);
+  delete S;
+  h->p2p_state = nullptr;
+  h->p2p = false;
+}
+
+void comm_p2p_unknown_predecessor(pfc_handle *h)
+{
+  if (h->p2p_state)
+    h->p2p_state->last_v = reinterpret_cast<const double *>(1);
+}
+
+// collective: every rank publishes IPC handles of its arena and sync block plus its layout; peers are mapped with
+// cudaIpcOpenMemHandle.  Any failure on any rank (no peer access, PFC_NO_P2P=1, more than 8 ranks) leaves all
+// ranks on the NCCL path.
+int comm_p2p_setup(pfc_handle *h)
+{
+  comm_p2p_destroy(h);
+  const Plan &P = h->plan;
+  NcclApi &n = nccl();
+  ncclComm_t comm = (ncclComm_t)h->comm;
+  cudaStream_t s = h->stream;
+  const int R = P.n_ranks, me = P.rank;
+  struct Card
+  {
+    cudaIpcMemHandle_t arena, sync;
+    int64_t Np, stride, sstride, offB, ok;
+    int64_t recv_off[kMaxRanksP2P]; // [source rank] start (nodes) of that rank's values in my ghost tail
+  };
+  static_assert(sizeof(Card) % 8 == 0, "Card is exchanged as int64 words");
+  Card mine;
+  std::memset(&mine, 0, sizeof(mine));
+  const char *env = getenv("PFC_NO_P2P");
+  bool ok = R <= kMaxRanksP2P && !(env && atoi(env) != 0);
+  P2PState *S = new P2PState();
+  S->R = R;
+  S->me = me;
+  P2PSync *sl = nullptr;
+  if (ok && cudaMalloc((void **)&sl, sizeof(P2PSync)) != cudaSuccess)
+    ok = false;
+  if (ok)
+    {
+      cudaMemsetAsync(sl, 0, sizeof(P2PSync), s);
+      cudaStreamSynchronize(s);
+      ok = cudaIpcGetMemHandle(&mine.arena, h->d_arena.p) == cudaSuccess &&
+           cudaIpcGetMemHandle(&mine.sync, sl) == cudaSuccess;
+    }
+  cudaGetLastError();
+  mine.Np = P.Np;
+  mine.stride = h->stride;
+  mine.sstride = h->sstride;
+  mine.offB = h->arena_off_scalar;
+  mine.ok = ok ? 1 : 0;
+  for (int q = 0; q < kMaxRanksP2P; ++q)
+    mine.recv_off[q] = -1;
+  for (size_t p = 0; p < P.peers.size(); ++p)
+    if (P.peers[p] < kMaxRanksP2P)
+      mine.recv_off[P.peers[p]] = P.recv_ptr[p];
+  std::vector<Card> all((size_t)R);
+  {
+    DevBuf<long long> d_mine, d_all;
+    const size_t words = sizeof(Card) / 8;
+    PFC_CUDA(h, d_mine.alloc(words));
+    PFC_CUDA(h, d_all.alloc(words * R));
+    PFC_CUDA(h, cudaMemcpyAsync(d_mine.p, &mine, sizeof(Card), cudaMemcpyHostToDevice, s));
+    PFC_NCCL(h, n.AllGather(d_mine.p, d_all.p, words, ncclInt64, comm, s));
+    PFC_CUDA(h, cudaMemcpyAsync(all.data(), d_all.p, sizeof(Card) * R, cudaMemcpyDeviceToHost, s));
+    PFC_CUDA(h, cudaStreamSynchronize(s));
+  }
+  for (int q = 0; q < R; ++q)
+    ok = ok && all[q].ok == 1;
+  if (ok)
+    for (int q = 0; q < R && ok; ++q)
+      {
+        S->Np[q] = all[q].Np;
+        S->stride[q] = all[q].stride;
+        S->sstride[q] = all[q].sstride;
+        S->offB[q] = all[q].offB;
+        S->recv_off[q] = all[q].recv_off[me];
+        if (q == me)
+          {
+            S->sync[q] = sl;
+            S->arena[q] = h->d_arena.p;
+            continue;
+          }
+        void *pa = nullptr, *ps = nullptr;
+        if (cudaIpcOpenMemHandle(&ps, all[q].sync, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
+          ok = false;
+        else
+          {
+            S->sync[q] = (P2PSync *)ps;
+            S->mapped_sync[q] = true;
+          }
+        if (ok && cudaIpcOpenMemHandle(&pa, all[q].arena, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
+          ok = false;
+        else if (ok)
+          {
+            S->arena[q] = (double *)pa;
+            S->mapped_arena[q] = true;
+          }
+      }
+  cudaGetLastError();
+  // agree on the outcome: one rank without peer access sends everybody to NCCL
+  {
+    DevBuf<long long> d_flag;
+    long long f = ok ? 1 : 0, fsum = 0;
+    PFC_CUDA(h, d_flag.alloc(1));
+    PFC_CUDA(h, cudaMemcpyAsync(d_flag.p, &f, sizeof(f), cudaMemcpyHostToDevice, s));
+    PFC_NCCL(h, n.AllReduce(d_flag.p, d_flag.p, 1, ncclInt64, ncclSum, comm, s));
+    PFC_CUDA(h, cudaMemcpyAsync(&fsum, d_flag.p, sizeof(fsum), cudaMemcpyDeviceToHost, s));
+    PFC_CUDA(h, cudaStreamSynchronize(s));
+    ok = fsum == R;
+  }
+  if (!S->sync[me])
+    S->sync[me] = sl;
+  h->p2p_state = S;
+  h->p2p = ok;
+  if (!ok)
+    comm_p2p_destroy(h);
   return PFC_OK;
 }
 } // namespace pfc

@@ -16,3 +16,12 @@ int halo_exchange(pfc_handle *h, double *v);           // v's ghost tail := owne
 int halo_exchange_scalar(pfc_handle *h, double *v);    // scalar field [owned Np | ghosts]
 int allreduce_sum(pfc_handle *h, double *dev, size_t n); // in place, stream-ordered; no-op on one rank
 } // namespace pfc
+
+// ---- peer-to-peer path (one node, NVLink): see pfc_comm.cu ------------------------------------------------
+namespace pfc
+{
+struct Ctl;
+int comm_p2p_setup(pfc_handle *h);     // after the arena exists; collective; h->p2p = false -> NCCL stays in charge
+void comm_p2p_destroy(pfc_handle *h);
+void comm_p2p_unknown_predecessor(pfc_handle *h); // before a graph capture / launch: force a flag-only round first
+} // namespace pfc

@@ -12,6 +12,10 @@
 #include "pfc_plan.h"
 
 struct ncclComm;
+namespace pfc
+{
+struct P2PState;
+}
 
 namespace pfc
 {
@@ -35,12 +39,22 @@ struct DevBuf
       return e;
     return cudaMemcpyAsync(p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, s);
   }
+  bool owns = true;
+  // non-owning window into another allocation (the peer-visible arena)
+  void view(T *ptr, size_t count)
+  {
+    release();
+    p = ptr;
+    n = count;
+    owns = false;
+  }
   void release()
   {
-    if (p)
+    if (p && owns)
       cudaFree(p);
     p = nullptr;
     n = 0;
+    owns = true;
   }
   ~DevBuf() { release(); }
   DevBuf() = default;
@@ -84,6 +98,14 @@ struct pfc_handle
   int comm_rank = 0, comm_size = 1;
   pfc::DevBuf<int32_t> d_send_rows;
   pfc::DevBuf<double> d_send_buf;
+  // every vector that takes part in a halo exchange lives in one allocation, so that peers can address it:
+  //   [n3 three-component vectors of `stride` doubles: Krylov basis, x, z, u | 12 scalar fields of `sstride`]
+  pfc::DevBuf<double> d_arena;
+  int64_t arena_off_scalar = 0; // doubles before the scalar fields
+  // peer-to-peer path over NVLink (pfc_comm.cu): ghost values are stored straight into the neighbours' vectors and
+  // small all-reduces go through per-rank slots, both synchronised by epoch flags in peer-visible memory
+  bool p2p = false;
+  pfc::P2PState *p2p_state = nullptr;
 
   // block-Schur preconditioner (pfc_precond.cuh)
   int64_t sstride = 0;                    // doubles between scalar work vectors (Np + n_ghost, rounded to 16)

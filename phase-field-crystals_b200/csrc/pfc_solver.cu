@@ -292,6 +292,7 @@ static int run_cycle(pfc_handle *h, bool first_cycle, bool two_pass)
       const int64_t before = h->launches;
       cudaGraph_t graph = nullptr;
       PFC_CUDA(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+      comm_p2p_unknown_predecessor(h);
       const int rc = enqueue_cycle(h, first_cycle, two_pass);
       cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
       if (rc != PFC_OK)
@@ -307,6 +308,7 @@ static int run_cycle(pfc_handle *h, bool first_cycle, bool two_pass)
       h->launches = before;                          // capture launched nothing
     }
   PFC_CUDA(h, cudaGraphLaunch(h->cycle_graph[gi], h->stream));
+  comm_p2p_unknown_predecessor(h);
   h->launches += h->graph_launches[gi];
   return PFC_OK;
 }
@@ -322,7 +324,8 @@ static int gmres_solve(pfc_handle *h, int64_t *iters, double *final_res)
   c0.max_iters = h->prm.gmres_max_iters > 0 ? h->prm.gmres_max_iters : P.n_dofs;
   *h->h_ctl = c0;
   PFC_CUDA(h, cudaMemcpyAsync(h->d_ctl.p, h->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, s));
-  PFC_CUDA(h, cudaMemsetAsync(h->d_x.p, 0, h->d_x.n * sizeof(double), s));
+  // owned part only: the ghost tail is written by the neighbours (p2p) and refreshed before every use
+  PFC_CUDA(h, cudaMemsetAsync(h->d_x.p, 0, 3 * P.Np * sizeof(double), s));
   PFC_CUDA(h, cudaStreamSynchronize(s)); // h_ctl is reused as the read-back buffer
   bool first = true, two_pass = h->prm.orthogonalization == PFC_ORTHO_CGS2;
   for (;;)
@@ -532,7 +535,7 @@ extern "C" int pfc_apply_operator(pfc_handle *h, const double *x, double *y)
   const int64_t n = P.n_dofs;
   const int blocks = (int)((n + 255) / 256);
   double *vx = h->d_V.p, *vy = h->d_V.p + h->stride;
-  PFC_CUDA(h, cudaMemsetAsync(vx, 0, h->stride * sizeof(double), h->stream));
+  PFC_CUDA(h, cudaMemsetAsync(vx, 0, 3 * P.Np * sizeof(double), h->stream));
   PFC_CUDA(h, cudaMemcpyAsync(h->d_io.p, x, n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
   scatter_kernel<<<blocks, 256, 0, h->stream>>>(vx, h->d_io.p, h->d_api_map.p, n);
   h->launches++;

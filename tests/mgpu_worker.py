@@ -34,6 +34,10 @@ def main():
     dist.broadcast_object_list(uid, src=0)
     s.comm_init(uid[0], rank, world)
     s.setup(mesh)
+    if rank == 0:
+        print(f"comm mode {s.comm_mode()} (1 NCCL, 2 peer memory)", flush=True)
+    if os.environ.get("PFC_REQUIRE_P2P") == "1" and os.environ.get("PFC_NO_P2P", "0") == "0":
+        assert s.comm_mode() == 2, "peer-memory path was not selected"
     Psi0 = mesh.hexagonal_lattice(P.default_A0(-0.43, -0.8), -0.43, [[2 * A, 0], [-2 * A, 0]], [[A, 0], [-A, 0]])
     s.set_state(Psi0, Psi0)
     if rank == 0:

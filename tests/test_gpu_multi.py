@@ -18,7 +18,11 @@ def _n_gpus():
                                                           (1, 5, 2, '{"preconditioner": 1}'), (2, 4, 1, '{"preconditioner": 1}'),
                                                           (1, 5, 2, '{"operator_kind": 1}'), (2, 4, 2, '{"operator_kind": 1, "preconditioner": 1}'),
                                                           (1, 5, 2, '{"operator_kind": 1, "preconditioner": 1}')])
-def test_ranks_match_oracle(built, degree, n_refines, steps, extra):
+@pytest.mark.parametrize("no_p2p", [0, 1])
+def test_ranks_match_oracle(built, degree, n_refines, steps, extra, no_p2p):
+    """no_p2p = 0: halo exchange and all-reduce by the peer-memory kernels over NVLink; 1: NCCL."""
+    if no_p2p and "operator_kind" not in extra and "preconditioner" not in extra and steps > 1:
+        pytest.skip("NCCL path covered by the other cases")
     n = _n_gpus()
     if n < 2:
         pytest.skip("needs >= 2 GPUs")
@@ -26,6 +30,7 @@ def test_ranks_match_oracle(built, degree, n_refines, steps, extra):
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
                "--master-addr", "127.0.0.1", "--master-port", "29517", os.path.join(ROOT, "tests", "mgpu_worker.py"),
                str(degree), str(n_refines), str(steps), extra]
-        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+        env = dict(os.environ, PFC_NO_P2P=str(no_p2p))
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
         print(r.stdout[-3000:])
         assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
