@@ -322,28 +322,25 @@ int halo_exchange_scalar(pfc_handle *h, double *v)
 }
 
 // =====================================================================================================
-// Peer-to-peer path over NVLink / NVSwitch (single node).  NCCL needs ~20 us per small operation and a
-// preconditioned GMRES iteration has ~16 of them; here
-//   * halo exchange = ONE kernel: every rank stores the values its neighbours need straight into the ghost
-//     tail of the neighbour's vector (peer-mapped with CUDA IPC), raises an epoch flag in the neighbour's
-//     memory (st.release.sys after a system fence) and waits for the neighbours' flags (ld.acquire.sys);
-//   * all-reduce of the <= 72 Gram-Schmidt coefficients = ONE single-CTA kernel: every rank stores its
-//     values into its slot on every rank, raises a flag, waits for the others and sums the slots in rank
-//     order, so all ranks hold bitwise identical results (fixed order).
-// Epochs are counted on the device (the kernels sit inside CUDA graphs that are replayed) and all ranks run
-// the same sequence of collective kernels.  Only two consecutive exchanges can overlap in time (a rank
-// cannot send exchange n+2 before it received n+1, which its neighbour sends after consuming n), so the
-// all-reduce slots are double buffered and a halo exchange on the same vector twice in a row is separated
-// by a flag-only round.
+// Peer-to-peer path over NVLink / NVSwitch (single node).  A preconditioned GMRES iteration has ~14 halo
+// exchanges and 2 all-reduces of a few doubles; what they cost is latency, not bandwidth.  Here both are ONE
+// kernel each, no fence and no separate flag: every double travels as one 16-byte store {lo, tag, hi, tag}
+// into a peer-mapped (CUDA IPC) buffer of the receiver, 8-byte halves are written atomically, and the
+// receiver polls the slot until both tags carry the current epoch (the scheme of NCCL's LL protocol).
+//   * halo exchange: store the values the neighbours need into their buffers, then poll the own buffer and
+//     unpack into the ghost tail of the vector (the consumer kernel follows in stream order);
+//   * all-reduce: store the <= 72 values into the own slot row on every rank, poll the rows of all ranks and
+//     sum them in rank order -> bitwise identical results on all ranks (fixed order).
+// Epochs are counted on the device (the kernels sit in CUDA graphs that are replayed) and all ranks run the
+// same sequence of collective kernels.  A rank cannot send exchange n+2 before it has received n+1, which
+// its neighbour sends after it has consumed n, so two buffer halves (epoch parity) are enough.
 // =====================================================================================================
 constexpr int kMaxRanksP2P = 8;
 constexpr int kArSlot = 72;
 
 struct P2PSync
 { // one per rank, peer-visible
-  unsigned long long halo_flag[kMaxRanksP2P]; // [source rank]: halo epochs completed by that rank
-  unsigned long long ar_flag[kMaxRanksP2P];
-  double ar_slot[2][kMaxRanksP2P][kArSlot];
+  uint4 ar_ll[2][kMaxRanksP2P][kArSlot]; // [epoch parity][source rank][value]
   unsigned long long halo_epoch, ar_epoch; // local
   unsigned int block_counter;
 };
@@ -351,21 +348,21 @@ struct P2PSync
 struct P2PState
 {
   int R = 0, me = 0;
-  P2PSync *sync[kMaxRanksP2P] = {};   // [rank]: mapped address (own: local allocation)
-  double *arena[kMaxRanksP2P] = {};
-  int64_t Np[kMaxRanksP2P] = {}, stride[kMaxRanksP2P] = {}, sstride[kMaxRanksP2P] = {}, offB[kMaxRanksP2P] = {};
-  int64_t recv_off[kMaxRanksP2P] = {}; // [rank q]: where my values start in q's ghost tail (nodes), -1 none
-  bool mapped_arena[kMaxRanksP2P] = {}, mapped_sync[kMaxRanksP2P] = {};
-  const double *last_v = nullptr;
+  P2PSync *sync[kMaxRanksP2P] = {}; // [rank]: mapped address (own: local allocation)
+  uint4 *ll[kMaxRanksP2P] = {};     // [rank]: halo buffer [2][3 n_ghost(rank)]
+  int64_t n_ghost[kMaxRanksP2P] = {};
+  int64_t recv_off[kMaxRanksP2P] = {}; // [rank q]: where my values start in q's ghost order (nodes), -1 none
+  bool mapped_ll[kMaxRanksP2P] = {}, mapped_sync[kMaxRanksP2P] = {};
 };
 
 struct P2PHaloArgs
 {
-  double *dst[kMaxRanksP2P];
-  unsigned long long *flag_peer[kMaxRanksP2P];       // peer's halo_flag[me]
-  const unsigned long long *flag_mine[kMaxRanksP2P]; // my halo_flag[peer]
+  uint4 *dst[kMaxRanksP2P];       // peer buffer, already offset to my first slot (parity 0)
+  int64_t half[kMaxRanksP2P];     // slots per parity half of that peer: 3 n_ghost(peer)
   int64_t send_ptr[kMaxRanksP2P + 1];
   int n_peers;
+  const uint4 *mine;              // own buffer
+  int64_t my_half, n_ghost;
 };
 
 struct P2PArArgs
@@ -374,60 +371,70 @@ struct P2PArArgs
   int R, me;
 };
 
-__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v)
+__device__ __forceinline__ unsigned int ll_tag(unsigned long long e) { return (unsigned int)(e & 0x7fffffffu) | 0x80000000u; }
+__device__ __forceinline__ void ll_store(uint4 *p, double v, unsigned int tag)
 {
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p)
-{
-  unsigned long long v;
-  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
+  const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"((unsigned int)b), "r"(tag),
+               "r"((unsigned int)(b >> 32)), "r"(tag)
+               : "memory");
 }
 // bounded wait: a peer that never arrives must not hang the GPU (trap -> CUDA error on the host)
-__device__ __forceinline__ void wait_flag(const unsigned long long *p, unsigned long long e)
+__device__ __forceinline__ double ll_wait(const uint4 *p, unsigned int tag)
 {
-  const long long t0 = clock64();
-  while (ld_acquire_sys(p) < e)
-    if (clock64() - t0 > 20000000000ll)
-      __trap();
+  unsigned int lo, t0, hi, t1;
+  const long long c0 = clock64();
+  for (;;)
+    {
+      asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(lo), "=r"(t0), "=r"(hi), "=r"(t1) : "l"(p) : "memory");
+      if (t0 == tag && t1 == tag)
+        break;
+      if (clock64() - c0 > 20000000000ll)
+        __trap();
+    }
+  return __longlong_as_double((long long)(((unsigned long long)hi << 32) | lo));
 }
 
+// grid is capped (all CTAs resident): every thread first stores all its values, then polls
 template <int NC>
-static __global__ void __launch_bounds__(256) p2p_halo_kernel(P2PHaloArgs H, const double *__restrict__ v,
+static __global__ void __launch_bounds__(256) p2p_halo_kernel(P2PHaloArgs H, double *__restrict__ v,
                                                                const int32_t *__restrict__ rows, int64_t Np,
                                                                P2PSync *sl, const Ctl *ctl)
 {
   if (ctl && ctl->state != 0)
     return;
-  __shared__ bool s_last;
-  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k < H.send_ptr[H.n_peers])
+  const unsigned long long e = sl->halo_epoch + 1;
+  const unsigned int tag = ll_tag(e);
+  const int64_t par = (int64_t)(e & 1);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  const int64_t n_send = H.send_ptr[H.n_peers];
+  for (int64_t k = tid; k < n_send; k += nth)
     {
       int p = 0;
       while (k >= H.send_ptr[p + 1])
         ++p;
       const int64_t j = k - H.send_ptr[p];
       const int32_t r = rows[k];
+      uint4 *d = H.dst[p] + par * H.half[p] + NC * j;
 #pragma unroll
       for (int c = 0; c < NC; ++c)
-        H.dst[p][NC * j + c] = v[(int64_t)c * Np + r];
+        ll_store(d + c, v[(int64_t)c * Np + r], tag);
     }
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0)
-    s_last = atomicAdd(&sl->block_counter, 1u) == gridDim.x - 1;
-  __syncthreads();
-  if (!s_last)
-    return;
-  const unsigned long long e = sl->halo_epoch + 1;
-  if ((int)threadIdx.x < H.n_peers)
+  const uint4 *m = H.mine + par * H.my_half;
+  for (int64_t g = tid; g < H.n_ghost; g += nth)
     {
-      st_release_sys(H.flag_peer[threadIdx.x], e);
-      wait_flag(H.flag_mine[threadIdx.x], e);
+      if (NC == 3)
+        {
+#pragma unroll
+          for (int c = 0; c < 3; ++c)
+            v[3 * Np + 3 * g + c] = ll_wait(m + 3 * g + c, tag);
+        }
+      else
+        v[Np + g] = ll_wait(m + g, tag);
     }
+  // the last CTA to finish advances the epoch (the next collective kernel starts after this one has ended)
   __syncthreads();
-  if (threadIdx.x == 0)
+  if (threadIdx.x == 0 && atomicAdd(&sl->block_counter, 1u) == gridDim.x - 1)
     {
       sl->halo_epoch = e;
       sl->block_counter = 0;
@@ -440,28 +447,19 @@ static __global__ void __launch_bounds__(128) p2p_allreduce_kernel(P2PArArgs A, 
   if (ctl && ctl->state != 0)
     return;
   const unsigned long long e = sl->ar_epoch + 1;
+  const unsigned int tag = ll_tag(e);
   const int b = (int)(e & 1), t = threadIdx.x;
   if (t < n)
     {
       const double val = dev[t];
       for (int q = 0; q < A.R; ++q)
-        A.sync[q]->ar_slot[b][A.me][t] = val;
-    }
-  __threadfence_system();
-  __syncthreads();
-  if (t < A.R && t != A.me)
-    {
-      st_release_sys(&A.sync[t]->ar_flag[A.me], e);
-      wait_flag(&sl->ar_flag[t], e);
-    }
-  __syncthreads();
-  if (t < n)
-    {
+        ll_store(&A.sync[q]->ar_ll[b][A.me][t], val, tag);
       double s = 0;
       for (int src = 0; src < A.R; ++src)
-        s += *(volatile const double *)&sl->ar_slot[b][src][t];
+        s += ll_wait(&sl->ar_ll[b][src][t], tag);
       dev[t] = s;
     }
+  __syncthreads();
   if (t == 0)
     sl->ar_epoch = e;
 }
@@ -485,53 +483,27 @@ static int p2p_halo(pfc_handle *h, double *v, int nc)
 {
   const Plan &P = h->plan;
   P2PState &S = *h->p2p_state;
-  const int64_t off = v - h->d_arena.p;
-  if (off < 0 || off >= (int64_t)h->d_arena.n)
-    return h->fail(PFC_ERR_NCCL, "p2p halo exchange of a vector outside the peer-visible arena");
-  int64_t slot;
-  if (nc == 3)
-    {
-      if (off >= h->arena_off_scalar || off % h->stride != 0)
-        return h->fail(PFC_ERR_NCCL, "p2p halo exchange: not a three-component arena vector");
-      slot = off / h->stride;
-    }
-  else
-    {
-      if (off < h->arena_off_scalar || (off - h->arena_off_scalar) % h->sstride != 0)
-        return h->fail(PFC_ERR_NCCL, "p2p halo exchange: not a scalar arena field");
-      slot = (off - h->arena_off_scalar) / h->sstride;
-    }
   P2PHaloArgs H;
   std::memset(&H, 0, sizeof(H));
   H.n_peers = (int)P.peers.size();
   for (int p = 0; p < H.n_peers; ++p)
     {
       const int q = P.peers[p];
-      const int64_t base = nc == 3 ? slot * S.stride[q] + 3 * S.Np[q] + 3 * std::max<int64_t>(S.recv_off[q], 0)
-                                   : S.offB[q] + slot * S.sstride[q] + S.Np[q] + std::max<int64_t>(S.recv_off[q], 0);
-      H.dst[p] = S.arena[q] + base;
-      H.flag_peer[p] = &S.sync[q]->halo_flag[S.me];
-      H.flag_mine[p] = &S.sync[S.me]->halo_flag[q];
+      H.half[p] = 3 * S.n_ghost[q];
+      H.dst[p] = S.ll[q] + (int64_t)nc * std::max<int64_t>(S.recv_off[q], 0);
       H.send_ptr[p] = P.send_ptr[p];
     }
   H.send_ptr[H.n_peers] = P.send_ptr[H.n_peers];
-  const int64_t ns = H.send_ptr[H.n_peers];
-  const int rounds = (v == S.last_v || S.last_v == reinterpret_cast<const double *>(1)) ? 2 : 1; // same vector twice in a row: flag-only round in between
-  for (int round = 0; round < rounds; ++round)
-    {
-      const bool flag_only = rounds == 2 && round == 0;
-      P2PHaloArgs G = H;
-      if (flag_only)
-        for (int p = 0; p <= H.n_peers; ++p)
-          G.send_ptr[p] = 0;
-      const int blocks = flag_only ? 1 : (int)std::max<int64_t>(1, (ns + 255) / 256);
-      if (nc == 3)
-        p2p_halo_kernel<3><<<blocks, 256, 0, h->stream>>>(G, v, h->d_send_rows.p, P.Np, S.sync[S.me], nullptr);
-      else
-        p2p_halo_kernel<1><<<blocks, 256, 0, h->stream>>>(G, v, h->d_send_rows.p, P.Np, S.sync[S.me], nullptr);
-      h->launches++;
-    }
-  S.last_v = v;
+  H.mine = S.ll[S.me];
+  H.my_half = 3 * P.n_ghost;
+  H.n_ghost = P.n_ghost;
+  const int64_t work = std::max<int64_t>(H.send_ptr[H.n_peers], P.n_ghost);
+  const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((work + 255) / 256, (int64_t)h->n_sm * 2));
+  if (nc == 3)
+    p2p_halo_kernel<3><<<blocks, 256, 0, h->stream>>>(H, v, h->d_send_rows.p, P.Np, S.sync[S.me], nullptr);
+  else
+    p2p_halo_kernel<1><<<blocks, 256, 0, h->stream>>>(H, v, h->d_send_rows.p, P.Np, S.sync[S.me], nullptr);
+  h->launches++;
   return PFC_OK;
 }
 
@@ -545,27 +517,25 @@ void comm_p2p_destroy(pfc_handle *h)
     cudaStreamSynchronize(h->stream);
   for (int q = 0; q < kMaxRanksP2P; ++q)
     {
-      if (S->mapped_arena[q])
-        cudaIpcCloseMemHandle(S->arena[q]);
+      if (S->mapped_ll[q])
+        cudaIpcCloseMemHandle(S->ll[q]);
       if (S->mapped_sync[q])
         cudaIpcCloseMemHandle(S->sync[q]);
     }
   if (S->sync[S->me])
     cudaFree(S->sync[S->me]);
+  if (S->ll[S->me])
+    cudaFree(S->ll[S->me]);
   delete S;
   h->p2p_state = nullptr;
   h->p2p = false;
 }
 
-void comm_p2p_unknown_predecessor(pfc_handle *h)
-{
-  if (h->p2p_state)
-    h->p2p_state->last_v = reinterpret_cast<const double *>(1);
-}
+void comm_p2p_unknown_predecessor(pfc_handle *) {} // the flag-in-data protocol needs no ordering hint
 
-// collective: every rank publishes IPC handles of its arena and sync block plus its layout; peers are mapped with
-// cudaIpcOpenMemHandle.  Any failure on any rank (no peer access, PFC_NO_P2P=1, more than 8 ranks) leaves all
-// ranks on the NCCL path.
+// collective: every rank publishes IPC handles of its halo buffer and sync block plus its ghost layout; peers are
+// mapped with cudaIpcOpenMemHandle.  Any failure on any rank (no peer access, PFC_NO_P2P=1, more than 8 ranks)
+// leaves all ranks on the NCCL path.
 int comm_p2p_setup(pfc_handle *h)
 {
   comm_p2p_destroy(h);
@@ -576,9 +546,9 @@ int comm_p2p_setup(pfc_handle *h)
   const int R = P.n_ranks, me = P.rank;
   struct Card
   {
-    cudaIpcMemHandle_t arena, sync;
-    int64_t Np, stride, sstride, offB, ok;
-    int64_t recv_off[kMaxRanksP2P]; // [source rank] start (nodes) of that rank's values in my ghost tail
+    cudaIpcMemHandle_t ll, sync;
+    int64_t n_ghost, ok;
+    int64_t recv_off[kMaxRanksP2P]; // [source rank] start (nodes) of that rank's values in my ghost order
   };
   static_assert(sizeof(Card) % 8 == 0, "Card is exchanged as int64 words");
   Card mine;
@@ -589,20 +559,21 @@ int comm_p2p_setup(pfc_handle *h)
   S->R = R;
   S->me = me;
   P2PSync *sl = nullptr;
-  if (ok && cudaMalloc((void **)&sl, sizeof(P2PSync)) != cudaSuccess)
+  uint4 *ll = nullptr;
+  const size_t ll_bytes = sizeof(uint4) * 2 * 3 * (size_t)std::max<int64_t>(P.n_ghost, 1);
+  if (ok && (cudaMalloc((void **)&sl, sizeof(P2PSync)) != cudaSuccess || cudaMalloc((void **)&ll, ll_bytes) != cudaSuccess))
     ok = false;
   if (ok)
     {
       cudaMemsetAsync(sl, 0, sizeof(P2PSync), s);
+      cudaMemsetAsync(ll, 0, ll_bytes, s);
       cudaStreamSynchronize(s);
-      ok = cudaIpcGetMemHandle(&mine.arena, h->d_arena.p) == cudaSuccess &&
-           cudaIpcGetMemHandle(&mine.sync, sl) == cudaSuccess;
+      ok = cudaIpcGetMemHandle(&mine.ll, ll) == cudaSuccess && cudaIpcGetMemHandle(&mine.sync, sl) == cudaSuccess;
     }
   cudaGetLastError();
-  mine.Np = P.Np;
-  mine.stride = h->stride;
-  mine.sstride = h->sstride;
-  mine.offB = h->arena_off_scalar;
+  S->sync[me] = sl;
+  S->ll[me] = ll;
+  mine.n_ghost = P.n_ghost;
   mine.ok = ok ? 1 : 0;
   for (int q = 0; q < kMaxRanksP2P; ++q)
     mine.recv_off[q] = -1;
@@ -625,18 +596,11 @@ int comm_p2p_setup(pfc_handle *h)
   if (ok)
     for (int q = 0; q < R && ok; ++q)
       {
-        S->Np[q] = all[q].Np;
-        S->stride[q] = all[q].stride;
-        S->sstride[q] = all[q].sstride;
-        S->offB[q] = all[q].offB;
+        S->n_ghost[q] = all[q].n_ghost;
         S->recv_off[q] = all[q].recv_off[me];
         if (q == me)
-          {
-            S->sync[q] = sl;
-            S->arena[q] = h->d_arena.p;
-            continue;
-          }
-        void *pa = nullptr, *ps = nullptr;
+          continue;
+        void *pl = nullptr, *ps = nullptr;
         if (cudaIpcOpenMemHandle(&ps, all[q].sync, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
           ok = false;
         else
@@ -644,12 +608,12 @@ int comm_p2p_setup(pfc_handle *h)
             S->sync[q] = (P2PSync *)ps;
             S->mapped_sync[q] = true;
           }
-        if (ok && cudaIpcOpenMemHandle(&pa, all[q].arena, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
+        if (ok && cudaIpcOpenMemHandle(&pl, all[q].ll, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess)
           ok = false;
         else if (ok)
           {
-            S->arena[q] = (double *)pa;
-            S->mapped_arena[q] = true;
+            S->ll[q] = (uint4 *)pl;
+            S->mapped_ll[q] = true;
           }
       }
   cudaGetLastError();
@@ -664,8 +628,6 @@ int comm_p2p_setup(pfc_handle *h)
     PFC_CUDA(h, cudaStreamSynchronize(s));
     ok = fsum == R;
   }
-  if (!S->sync[me])
-    S->sync[me] = sl;
   h->p2p_state = S;
   h->p2p = ok;
   if (!ok)
