@@ -15,21 +15,39 @@ namespace
 // cells per CTA (one thread per cell); the inner (CX-1) x (CY-1) cells are the CTA's own
 constexpr int kCX = 16, kCY = 16;
 
-template <int P, int MODE>
-int launch_mode(pfc_handle *h, const LatOp &op, const Ctl *ctl)
+template <int P, int MODE, int CX, int CY>
+int launch_tile(pfc_handle *h, const LatOp &op, const Ctl *ctl)
 {
+  static bool opted_in = false; // per instantiation; one device per process (one rank per GPU)
+  if (!opted_in)
+    {
+      PFC_CUDA(h, cudaFuncSetAttribute(lat_kernel<P, MODE, CX, CY>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)lat_smem_bytes<P, MODE, CX, CY>()));
+      opted_in = true;
+    }
   const LatGeom &G = h->lat_geom;
-  const dim3 grid((G.ncx + kCX - 2) / (kCX - 1), (G.ncy + kCY - 2) / (kCY - 1));
-  lat_kernel<P, MODE, kCX, kCY><<<grid, kCX * kCY, lat_smem_bytes<P, MODE, kCX, kCY>(), h->stream>>>(G, op, ctl);
+  const dim3 grid((G.ncx + CX - 2) / (CX - 1), (G.ncy + CY - 2) / (CY - 1));
+  lat_kernel<P, MODE, CX, CY><<<grid, CX * CY, lat_smem_bytes<P, MODE, CX, CY>(), h->stream>>>(G, op, ctl);
   h->launches++;
   return PFC_OK;
 }
 
 template <int P, int MODE>
-cudaError_t opt_in_smem()
+int launch_mode(pfc_handle *h, const LatOp &op, const Ctl *ctl)
 {
-  return cudaFuncSetAttribute(lat_kernel<P, MODE, kCX, kCY>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)lat_smem_bytes<P, MODE, kCX, kCY>());
+  if constexpr (MODE == LAT_J || MODE == LAT_S)
+    { // the two hot cell kernels: 16 x 8 cells per CTA for Q2 (two CTAs per SM instead of one: J 49 -> 35 us, Schur row
+      // 30 -> 27 us on M2), 16 x 16 for Q1; PFC_LAT_TILE overrides (tuning aid, profiles/tile_sweep.sh)
+      static const int tile = getenv("PFC_LAT_TILE") ? atoi(getenv("PFC_LAT_TILE")) : -1;
+      switch (tile >= 0 ? tile : (P == 2 ? 1 : 0))
+        {
+        case 1: return launch_tile<P, MODE, 16, 8>(h, op, ctl);
+        case 2: return launch_tile<P, MODE, 32, 8>(h, op, ctl);
+        case 3: return launch_tile<P, MODE, 8, 8>(h, op, ctl);
+        default: break;
+        }
+    }
+  return launch_tile<P, MODE, kCX, kCY>(h, op, ctl);
 }
 } // namespace
 
@@ -59,18 +77,27 @@ int lat_launch(pfc_handle *h, int mode, const LatOp &op, const Ctl *ctl)
     else                                                                                 \
       lat_kstencil_kernel<2, KX, KY><<<grid, KX, 0, h->stream>>>(G, op, ctl);            \
   }
+#define PFC_KS2(KX, KY)                                                                  \
+  {                                                                                      \
+    const dim3 grid((G.w + 2 * KX - 1) / (2 * KX), (G.h + KY - 1) / KY);                 \
+    if (q1)                                                                              \
+      lat_kstencil2_kernel<1, KX, KY><<<grid, KX, 0, h->stream>>>(G, op, ctl);           \
+    else                                                                                 \
+      lat_kstencil2_kernel<2, KX, KY><<<grid, KX, 0, h->stream>>>(G, op, ctl);           \
+  }
       switch (variant)
         {
-        case 1: PFC_KS(128, 2) break;
+        case 10: PFC_KS2(64, 4) break;
+        case 11: PFC_KS2(128, 4) break;
+        case 12: PFC_KS2(64, 8) break;
+        case 13: PFC_KS2(64, 2) break;
+        case 14: PFC_KS2(32, 4) break;
         case 2: PFC_KS(128, 8) break;
-        case 3: PFC_KS(128, 16) break;
-        case 4: PFC_KS(64, 4) break;
-        case 5: PFC_KS(256, 4) break;
         case 6: PFC_KS(64, 8) break;
-        case 7: PFC_KS(256, 1) break;
         default: PFC_KS(128, 4) break;
         }
 #undef PFC_KS
+#undef PFC_KS2
       h->launches++;
       return PFC_OK;
     }
@@ -174,14 +201,8 @@ int lat_setup(pfc_handle *h)
   G.Np = h->plan.Np;
   G.hx = L.hx;
   G.hy = L.hy;
-  PFC_CUDA(h, (opt_in_smem<1, LAT_J>()));
-  PFC_CUDA(h, (opt_in_smem<1, LAT_S>()));
-  PFC_CUDA(h, (opt_in_smem<1, LAT_K>()));
-  PFC_CUDA(h, (opt_in_smem<1, LAT_R>()));
-  PFC_CUDA(h, (opt_in_smem<2, LAT_J>()));
-  PFC_CUDA(h, (opt_in_smem<2, LAT_S>()));
-  PFC_CUDA(h, (opt_in_smem<2, LAT_K>()));
-  PFC_CUDA(h, (opt_in_smem<2, LAT_R>()));
+  G.ihx = 1.0 / L.hx;
+  G.ihy = 1.0 / L.hy;
   if (h->d_inv_ml.n != (size_t)h->plan.Np)
     PFC_CUDA(h, h->d_inv_ml.alloc(h->plan.Np));
   if (h->d_dinvB.n != (size_t)h->plan.Np)

@@ -269,7 +269,7 @@ static __global__ void __launch_bounds__(CX *CY) lat_kernel(LatGeom L, LatOp O, 
   const int cx = tid % CX, cy = tid / CX;
   const int kx = ax0 - 1 + cx, ky = ay0 - 1 + cy;
   const bool cell_ok = kx >= 0 && kx < L.ncx && ky >= 0 && ky < L.ncy;
-  const double hx = L.hx, hy = L.hy, ihx = 1.0 / hx, ihy = 1.0 / hy, vol = hx * hy;
+  const double hx = L.hx, hy = L.hy, ihx = L.ihx, ihy = L.ihy, vol = hx * hy;
   const double *cell_in = s_in + (P * cy) * TNX + P * cx;
   auto load_u = [&](int f, double(&u)[n][n]) {
 #pragma unroll
@@ -527,12 +527,40 @@ static __global__ void __launch_bounds__(CX *CY) lat_kernel(LatGeom L, LatOp O, 
       lat_test<P, true, true>(cf0, cfx, cfy, ihx, ihy, y0);
       store_y(0, y0);
     }
-  __syncthreads();
-
   // ---- nodes of the inner cells: gather the local results in a fixed order, fused epilogue ----
-  constexpr int ONX = P * (CX - 1), ONY = P * (CY - 1);
-  for (int idx = tid; idx < ONX * ONY; idx += NT)
+  constexpr int ONX = P * (CX - 1), ONY = P * (CY - 1), EIT = (ONX * ONY + NT - 1) / NT;
+  // epilogue operands of the Schur-row modes are fetched before the barrier, so their latency overlaps the wait
+  double e_add[EIT], e_d[EIT], e_dinv[EIT], e_s0[EIT];
+  if constexpr (MODE == LAT_S)
     {
+#pragma unroll
+      for (int it = 0; it < EIT; ++it)
+        {
+          const int idx = tid + it * NT;
+          const int lx = nx0 + P + idx % ONX - L.ex0, ly = ny0 + P + idx / ONX - L.ey0;
+          e_add[it] = e_d[it] = e_dinv[it] = e_s0[it] = 0.0;
+          if (idx < ONX * ONY && (unsigned)lx < (unsigned)L.w && (unsigned)ly < (unsigned)L.h)
+            {
+              const int64_t r = (int64_t)ly * L.w + lx;
+              if (O.epi != 2)
+                e_add[it] = O.add[r];
+              if (O.epi == 1)
+                {
+                  e_d[it] = O.d[r];
+                  e_s0[it] = O.s0[r];
+                }
+              if (O.epi != 0 || O.d)
+                e_dinv[it] = O.dinv[r];
+            }
+        }
+    }
+  __syncthreads();
+#pragma unroll
+  for (int it = 0; it < EIT; ++it)
+    {
+      const int idx = tid + it * NT;
+      if (idx >= ONX * ONY)
+        break;
       const int i = P + idx % ONX, j = P + idx / ONX; // tile node
       const int lx = nx0 + i - L.ex0, ly = ny0 + j - L.ey0;
       if ((unsigned)lx >= (unsigned)L.w || (unsigned)ly >= (unsigned)L.h)
@@ -575,16 +603,25 @@ static __global__ void __launch_bounds__(CX *CY) lat_kernel(LatGeom L, LatOp O, 
       else if constexpr (MODE == LAT_S)
         {
           if (O.epi == 0)
-            O.out[r] = O.add[r] + val[0];
+            {
+              const double rhs = e_add[it] + val[0];
+              O.out[r] = rhs;
+              if (O.d)
+                { // first Chebyshev step fused: d = x = dinv rhs / theta
+                  const double x0 = O.cheb[0] * e_dinv[it] * rhs;
+                  O.d[r] = x0;
+                  O.out2[r] = x0;
+                }
+            }
           else if (O.epi == 1)
             {
-              const double res = O.add[r] - val[0];
-              const double dn = O.cheb[0] * O.d[r] + O.cheb[1] * O.dinv[r] * res;
+              const double res = e_add[it] - val[0];
+              const double dn = O.cheb[0] * e_d[it] + O.cheb[1] * e_dinv[it] * res;
               O.d[r] = dn;
-              O.out[r] = O.s0[r] + dn;
+              O.out[r] = e_s0[it] + dn;
             }
           else
-            O.out[r] = O.dinv[r] * val[0];
+            O.out[r] = e_dinv[it] * val[0];
         }
       else
         {
@@ -642,7 +679,7 @@ static __global__ void __launch_bounds__(kKsX) lat_kstencil_kernel(LatGeom L, La
   double kx[2 * P + 1], mx[2 * P + 1];
   sfor<2 * P + 1>([&](auto DD) {
     PFC_IC(dd, DD);
-    kx[dd] = (midx ? Row1<P>::K(1, dd - P) : Row1<P>::K(0, dd - P)) / L.hx;
+    kx[dd] = (midx ? Row1<P>::K(1, dd - P) : Row1<P>::K(0, dd - P)) * L.ihx;
     mx[dd] = (midx ? Row1<P>::M(1, dd - P) : Row1<P>::M(0, dd - P)) * L.hx;
   });
   double rK[R], rM[R];
@@ -695,7 +732,7 @@ static __global__ void __launch_bounds__(kKsX) lat_kstencil_kernel(LatGeom L, La
       sfor<2 * P + 1>([&](auto DD) {
         PFC_IC(dd, DD);
         const double my = (midy ? Row1<P>::M(1, dd - P) : Row1<P>::M(0, dd - P)) * L.hy;
-        const double ky = (midy ? Row1<P>::K(1, dd - P) : Row1<P>::K(0, dd - P)) / L.hy;
+        const double ky = (midy ? Row1<P>::K(1, dd - P) : Row1<P>::K(0, dd - P)) * L.ihy;
         s = fma(my, rK[j + dd], s);
         s = fma(ky, rM[j + dd], s);
       });
@@ -707,6 +744,131 @@ static __global__ void __launch_bounds__(kKsX) lat_kstencil_kernel(LatGeom L, La
       O.out[r] = res;
       if (O.out2)
         O.out2[r] = res;
+    }
+}
+
+// Two columns per thread: the 2 p + 1 wide row supports of columns lx and lx + 1 lie in x[lx - 2 .. lx + 3], i.e.
+// three aligned 16-byte loads per row instead of 2 (2 p + 1) 8-byte loads (the one-column kernel is bound by
+// load instructions, not bytes).  lx is even, w even on the fast path.
+template <int P, int KX, int KY>
+static __global__ void __launch_bounds__(KX) lat_kstencil2_kernel(LatGeom L, LatOp O, const Ctl *ctl)
+{
+  if (ctl && ctl->state != 0)
+    return;
+  constexpr int R = KY + 2 * P, NW = 2 * P + 1;
+  const int lx = 2 * (blockIdx.x * KX + threadIdx.x), ly0 = blockIdx.y * KY;
+  if (lx >= L.w)
+    return;
+  const double *__restrict__ v = O.s0;
+  // column A = lx, column B = lx + 1: vertex / mid alternate for Q2
+  const int midA = (P == 2) ? ((L.ex0 + lx) & 1) : 0, midB = (P == 2) ? (midA ^ 1) : 0;
+  double kA[NW], mA[NW], kB[NW], mB[NW];
+  sfor<NW>([&](auto DD) {
+    PFC_IC(dd, DD);
+    kA[dd] = (midA ? Row1<P>::K(1, dd - P) : Row1<P>::K(0, dd - P)) * L.ihx;
+    mA[dd] = (midA ? Row1<P>::M(1, dd - P) : Row1<P>::M(0, dd - P)) * L.hx;
+    kB[dd] = (midB ? Row1<P>::K(1, dd - P) : Row1<P>::K(0, dd - P)) * L.ihx;
+    mB[dd] = (midB ? Row1<P>::M(1, dd - P) : Row1<P>::M(0, dd - P)) * L.hx;
+  });
+  double rKA[R], rMA[R], rKB[R], rMB[R];
+  const bool fast = (L.w & 1) == 0 && lx - 2 >= 0 && lx + 3 < L.w && ly0 - P >= 0 && ly0 + KY - 1 + P < L.h;
+  if (fast)
+    {
+      const double2 *p0 = reinterpret_cast<const double2 *>(v + (int64_t)(ly0 - P) * L.w + lx - 2);
+      const int64_t w2 = L.w >> 1;
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        {
+          const double2 a = __ldg(p0 + r * w2), b = __ldg(p0 + r * w2 + 1), c = __ldg(p0 + r * w2 + 2);
+          const double val[6] = {a.x, a.y, b.x, b.y, c.x, c.y};
+          double ska = 0, sma = 0, skb = 0, smb = 0;
+#pragma unroll
+          for (int dd = 0; dd < NW; ++dd)
+            {
+              ska = fma(kA[dd], val[2 + dd - P], ska);
+              sma = fma(mA[dd], val[2 + dd - P], sma);
+              skb = fma(kB[dd], val[3 + dd - P], skb);
+              smb = fma(mB[dd], val[3 + dd - P], smb);
+            }
+          rKA[r] = ska, rMA[r] = sma, rKB[r] = skb, rMB[r] = smb;
+        }
+    }
+  else
+    {
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        {
+          const int ey = min(max(L.ey0 + ly0 - P + r, 0), L.fh - 1);
+          double val[6];
+#pragma unroll
+          for (int k = 0; k < 6; ++k)
+            val[k] = v[lat_id(L, min(max(L.ex0 + lx - 2 + k, 0), L.fw - 1), ey)];
+          double ska = 0, sma = 0, skb = 0, smb = 0;
+#pragma unroll
+          for (int dd = 0; dd < NW; ++dd)
+            {
+              ska = fma(kA[dd], val[2 + dd - P], ska);
+              sma = fma(mA[dd], val[2 + dd - P], sma);
+              skb = fma(kB[dd], val[3 + dd - P], skb);
+              smb = fma(mB[dd], val[3 + dd - P], smb);
+            }
+          rKA[r] = ska, rMA[r] = sma, rKB[r] = skb, rMB[r] = smb;
+        }
+    }
+  const bool hasB = lx + 1 < L.w;
+#pragma unroll
+  for (int j = 0; j < KY; ++j)
+    {
+      const int ly = ly0 + j;
+      if (ly >= L.h)
+        break;
+      const int midy = (P == 2) ? ((L.ey0 + ly) & 1) : 0;
+      double sa = 0, sb = 0;
+      sfor<NW>([&](auto DD) {
+        PFC_IC(dd, DD);
+        const double my = (midy ? Row1<P>::M(1, dd - P) : Row1<P>::M(0, dd - P)) * L.hy;
+        const double ky = (midy ? Row1<P>::K(1, dd - P) : Row1<P>::K(0, dd - P)) * L.ihy;
+        sa = fma(my, rKA[j + dd], sa);
+        sa = fma(ky, rMA[j + dd], sa);
+        sb = fma(my, rKB[j + dd], sb);
+        sb = fma(ky, rMB[j + dd], sb);
+      });
+      const int64_t r = (int64_t)ly * L.w + lx;
+      double ra = O.k * sa, rb = O.k * sb;
+      if (fast)
+        {
+          if (O.add)
+            {
+              const double2 ad = *reinterpret_cast<const double2 *>(O.add + r);
+              ra += O.a * ad.x;
+              rb += O.a * ad.y;
+            }
+          const double2 im = *reinterpret_cast<const double2 *>(O.inv_ml + r);
+          const double2 res = make_double2(ra * im.x, rb * im.y);
+          *reinterpret_cast<double2 *>(O.out + r) = res;
+          if (O.out2)
+            *reinterpret_cast<double2 *>(O.out2 + r) = res;
+        }
+      else
+        {
+          if (O.add)
+            {
+              ra += O.a * O.add[r];
+              if (hasB)
+                rb += O.a * O.add[r + 1];
+            }
+          ra *= O.inv_ml[r];
+          O.out[r] = ra;
+          if (O.out2)
+            O.out2[r] = ra;
+          if (hasB)
+            {
+              rb *= O.inv_ml[r + 1];
+              O.out[r + 1] = rb;
+              if (O.out2)
+                O.out2[r + 1] = rb;
+            }
+        }
     }
 }
 

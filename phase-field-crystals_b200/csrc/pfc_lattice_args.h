@@ -14,7 +14,7 @@ struct LatGeom
   int32_t ncx, ncy, ex0, ey0, w, h, fw, fh;
   const int32_t *lut;
   int64_t Np;
-  double hx, hy;
+  double hx, hy, ihx, ihy; // cell size and its reciprocals
 };
 
 enum

@@ -234,10 +234,33 @@ int precond_apply(pfc_handle *h, const double *in, double *out, const Ctl *ctl)
   PFC_TRY(halo_exchange_scalar(h, m1));
   run_kmv(h, S, nb, r2, 1.0, m1, -1.0, t, nullptr, ctl);                // t = M_L^-1 (r2 - K m1)
   PFC_TRY(halo_exchange_scalar(h, t));
-  run_bcd<0>(h, S, nb, nullptr, m1, t, 0.0, -1.0, -1.0, r0, nullptr, nullptr, nullptr, rhs, ctl);
-  // Chebyshev on S_L psi = rhs, Jacobi scaling diag(B)^-1
-  vec_mul_kernel<<<g, 256, 0, s>>>(d, xa, 1.0, h->d_cheb.p, rhs, h->d_dinvB.p, Np, ctl);            // d = x = dinv rhs / theta
-  h->launches += 4;
+  // Schur right-hand side rhs = r0 - C m1 - D t, then Chebyshev on S_L psi = rhs with Jacobi scaling diag(B)^-1:
+  // first step d = x = dinv rhs / theta (fused into the epilogue of the lattice kernel)
+  if (h->lat)
+    {
+      LatOp op = lat_op(h);
+      op.in3b = h->d_psi_n.p;
+      op.s1 = m1;
+      op.s2 = t;
+      op.sB = 0.0;
+      op.sC = -1.0;
+      op.sD = -1.0;
+      op.add = r0;
+      op.dinv = h->d_dinvB.p;
+      op.cheb = h->d_cheb.p;
+      op.d = d;
+      op.out = rhs;
+      op.out2 = xa;
+      op.epi = 0;
+      PFC_TRY(lat_launch(h, LAT_S, op, ctl));
+      h->launches += 2;
+    }
+  else
+    {
+      run_bcd<0>(h, S, nb, nullptr, m1, t, 0.0, -1.0, -1.0, r0, nullptr, nullptr, nullptr, rhs, ctl);
+      vec_mul_kernel<<<g, 256, 0, s>>>(d, xa, 1.0, h->d_cheb.p, rhs, h->d_dinvB.p, Np, ctl);          // d = x = dinv rhs / theta
+      h->launches += 4;
+    }
   double *x = xa, *xn = xb;
   for (int i = 1; i < h->sweeps; ++i)
     {
