@@ -167,7 +167,7 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--degree", type=int, default=2)
@@ -234,6 +234,7 @@ def main():
     # ---- device-resident loop: W warm-up steps, then K timed steps (CUDA events inside pfc_step) ----
     for _ in range(args.warmup):
         solver.step()
+    start_state = solver.get_state()  # the e2e loop below replays the same K steps from here
     stats = []
     barrier()
     with ClockSampler(local) as clk:
@@ -245,17 +246,17 @@ def main():
     ms_dev = sum(s["ms_total"] for s in stats)
     launches = sum(s["kernel_launches"] for s in stats)
     # ---- e2e: host buffers in, host buffers out, every step (state upload + step + psi download) ----
-    out = torch.empty(n_dofs, dtype=torch.float64).pin_memory().numpy()
-    cur = solver.get_state(want_n1=True)
-    pin_np[0], pin_np[1] = cur[0], cur[1]
+    # pinned ping-pong buffers: the state downloaded after step k is the state uploaded for step k + 1
+    # (Psi_n_1 = Psi_n after a step, mpi.cpp:592)
+    outs = [torch.empty(n_dofs, dtype=torch.float64).pin_memory().numpy() for _ in range(2)]
+    outs[0][:] = start_state
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        solver.set_state(pin_np[0], pin_np[1])
+    for k in range(args.steps):
+        src, dst = outs[k & 1], outs[(k + 1) & 1]
+        solver.set_state(src, src)
         st = solver.step()
-        launches_e2e = st["kernel_launches"]
-        solver.get_state(out_n=out)
-        pin_np[0], pin_np[1] = out, out
+        solver.get_state(out_n=dst)
     barrier()
     t_e2e = time.perf_counter() - t0
 
@@ -291,7 +292,7 @@ def main():
                        "newton_assemblies_per_step": [s["n_assemblies"] for s in stats], "gmres_iters_per_step": its},
             "ms_wall_per_step": ms_wall / args.steps,
             "e2e": {"value": n_dofs * args.steps / (ms_e2e * 1e-3), "unit": "DoF-steps/s",
-                    "h2d_bytes_per_step": int(2 * n_dofs * 8), "d2h_bytes_per_step": int(n_dofs * 8)},
+                    "h2d_bytes_per_step": int(n_dofs * 8), "d2h_bytes_per_step": int(n_dofs * 8)},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": ("lat_kernel<LAT_J> (y = J x matrix-free on the tensor lattice)" if args.mf else
                                     "spmv_sell_kernel (y = J x, shared-pattern SELL-32 block layout)"),

@@ -304,7 +304,8 @@ extern "C" int pfc_set_state(pfc_handle *h, const double *Psi_n, const double *P
   double *dst[2] = {h->d_psi_n.p, h->d_psi_n1.p};
   for (int k = 0; k < 2; ++k)
     {
-      PFC_CUDA(h, cudaMemcpyAsync(h->d_io.p, src[k], n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+      if (k == 0 || src[1] != src[0]) // same host array for both time levels: one upload, two scatters
+        PFC_CUDA(h, cudaMemcpyAsync(h->d_io.p, src[k], n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
       scatter_kernel<<<blocks, 256, 0, h->stream>>>(dst[k], h->d_io.p, h->d_api_map.p, n);
       h->launches++;
     }
