@@ -93,7 +93,8 @@ extern "C" int pfc_create(const pfc_params *p, pfc_handle **out)
   h->prm.gmres_n_tmp_vectors = ntmp;
   h->restart = ntmp - 2;
   h->n_basis = ntmp - 1;
-  h->sweeps = p->precond_sweeps > 0 ? p->precond_sweeps : 4;
+  // Chebyshev degree: measured optimum of the lattice path on M2-sized meshes (profiles/README.md): Q2 5, Q1 3
+  h->sweeps = p->precond_sweeps > 0 ? p->precond_sweeps : (p->degree == 2 ? 5 : 3);
   int dev = p->device;
   if (dev < 0)
     cudaGetDevice(&dev);

@@ -173,8 +173,8 @@ extern "C" int pfc_comm_init(pfc_handle *h, const void *id_bytes128, int rank, i
 
 namespace pfc
 {
-static int p2p_allreduce(pfc_handle *h, double *dev, size_t n);
-static int p2p_halo(pfc_handle *h, double *v, int nc);
+static int p2p_allreduce(pfc_handle *h, double *dev, size_t n, const Ctl *ctl);
+static int p2p_halo(pfc_handle *h, double *v, int nc, const Ctl *ctl);
 
 void comm_destroy(pfc_handle *h)
 {
@@ -188,12 +188,12 @@ void comm_destroy(pfc_handle *h)
   h->comm_size = 1;
 }
 
-int allreduce_sum(pfc_handle *h, double *dev, size_t n)
+int allreduce_sum(pfc_handle *h, double *dev, size_t n, const Ctl *ctl)
 {
   if (h->comm_size <= 1)
     return PFC_OK;
   if (h->p2p)
-    return p2p_allreduce(h, dev, n);
+    return p2p_allreduce(h, dev, n, ctl);
   PFC_NCCL(h, nccl().AllReduce(dev, dev, n, ncclDouble, ncclSum, (ncclComm_t)h->comm, h->stream));
   return PFC_OK;
 }
@@ -265,13 +265,13 @@ int comm_exchange_send_lists(pfc_handle *h)
   return PFC_OK;
 }
 
-int halo_exchange(pfc_handle *h, double *v)
+int halo_exchange(pfc_handle *h, double *v, const Ctl *ctl)
 {
   const Plan &P = h->plan;
   if (P.n_ranks <= 1)
     return PFC_OK;
   if (h->p2p)
-    return p2p_halo(h, v, 3);
+    return p2p_halo(h, v, 3, ctl);
   NcclApi &n = nccl();
   ncclComm_t comm = (ncclComm_t)h->comm;
   const int64_t ns = (int64_t)P.send_rows.size();
@@ -293,13 +293,13 @@ int halo_exchange(pfc_handle *h, double *v)
   return PFC_OK;
 }
 
-int halo_exchange_scalar(pfc_handle *h, double *v)
+int halo_exchange_scalar(pfc_handle *h, double *v, const Ctl *ctl)
 {
   const Plan &P = h->plan;
   if (P.n_ranks <= 1)
     return PFC_OK;
   if (h->p2p)
-    return p2p_halo(h, v, 1);
+    return p2p_halo(h, v, 1, ctl);
   NcclApi &n = nccl();
   ncclComm_t comm = (ncclComm_t)h->comm;
   const int64_t ns = (int64_t)P.send_rows.size();
@@ -464,7 +464,7 @@ static __global__ void __launch_bounds__(128) p2p_allreduce_kernel(P2PArArgs A, 
     sl->ar_epoch = e;
 }
 
-static int p2p_allreduce(pfc_handle *h, double *dev, size_t n)
+static int p2p_allreduce(pfc_handle *h, double *dev, size_t n, const Ctl *ctl)
 {
   P2PState &S = *h->p2p_state;
   if (n > (size_t)kArSlot)
@@ -474,12 +474,12 @@ static int p2p_allreduce(pfc_handle *h, double *dev, size_t n)
     A.sync[q] = S.sync[q];
   A.R = S.R;
   A.me = S.me;
-  p2p_allreduce_kernel<<<1, 128, 0, h->stream>>>(A, dev, (int)n, S.sync[S.me], nullptr);
+  p2p_allreduce_kernel<<<1, 128, 0, h->stream>>>(A, dev, (int)n, S.sync[S.me], ctl);
   h->launches++;
   return PFC_OK;
 }
 
-static int p2p_halo(pfc_handle *h, double *v, int nc)
+static int p2p_halo(pfc_handle *h, double *v, int nc, const Ctl *ctl)
 {
   const Plan &P = h->plan;
   P2PState &S = *h->p2p_state;
@@ -500,9 +500,9 @@ static int p2p_halo(pfc_handle *h, double *v, int nc)
   const int64_t work = std::max<int64_t>(H.send_ptr[H.n_peers], P.n_ghost);
   const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((work + 255) / 256, (int64_t)h->n_sm * 2));
   if (nc == 3)
-    p2p_halo_kernel<3><<<blocks, 256, 0, h->stream>>>(H, v, h->d_send_rows.p, P.Np, S.sync[S.me], nullptr);
+    p2p_halo_kernel<3><<<blocks, 256, 0, h->stream>>>(H, v, h->d_send_rows.p, P.Np, S.sync[S.me], ctl);
   else
-    p2p_halo_kernel<1><<<blocks, 256, 0, h->stream>>>(H, v, h->d_send_rows.p, P.Np, S.sync[S.me], nullptr);
+    p2p_halo_kernel<1><<<blocks, 256, 0, h->stream>>>(H, v, h->d_send_rows.p, P.Np, S.sync[S.me], ctl);
   h->launches++;
   return PFC_OK;
 }

@@ -10,11 +10,14 @@ struct pfc_handle;
 
 namespace pfc
 {
+struct Ctl;
+// ctl (optional): the peer-memory kernels skip themselves once the solve has ended (Ctl.state != 0 is identical on all
+// ranks: it derives from all-reduced values); NCCL operations always run
 void comm_destroy(pfc_handle *h);
 int comm_exchange_send_lists(pfc_handle *h);           // after build_plan: fills plan.send_ptr / send_rows
-int halo_exchange(pfc_handle *h, double *v);           // v's ghost tail := owners' values (stream-ordered)
-int halo_exchange_scalar(pfc_handle *h, double *v);    // scalar field [owned Np | ghosts]
-int allreduce_sum(pfc_handle *h, double *dev, size_t n); // in place, stream-ordered; no-op on one rank
+int halo_exchange(pfc_handle *h, double *v, const Ctl *ctl = nullptr);           // v's ghost tail := owners' values (stream-ordered)
+int halo_exchange_scalar(pfc_handle *h, double *v, const Ctl *ctl = nullptr);    // scalar field [owned Np | ghosts]
+int allreduce_sum(pfc_handle *h, double *dev, size_t n, const Ctl *ctl = nullptr); // in place, stream-ordered; no-op on one rank
 } // namespace pfc
 
 // ---- peer-to-peer path (one node, NVLink): see pfc_comm.cu ------------------------------------------------

@@ -231,9 +231,9 @@ int precond_apply(pfc_handle *h, const double *in, double *out, const Ctl *ctl)
   const double *iml = h->d_inv_ml.p;
 
   vec_mul_kernel<<<g, 256, 0, s>>>(m1, nullptr, 1.0, nullptr, r1, iml, Np, ctl);                     // m1 = M_L^-1 r1
-  PFC_TRY(halo_exchange_scalar(h, m1));
+  PFC_TRY(halo_exchange_scalar(h, m1, ctl));
   run_kmv(h, S, nb, r2, 1.0, m1, -1.0, t, nullptr, ctl);                // t = M_L^-1 (r2 - K m1)
-  PFC_TRY(halo_exchange_scalar(h, t));
+  PFC_TRY(halo_exchange_scalar(h, t, ctl));
   // Schur right-hand side rhs = r0 - C m1 - D t, then Chebyshev on S_L psi = rhs with Jacobi scaling diag(B)^-1:
   // first step d = x = dinv rhs / theta (fused into the epilogue of the lattice kernel)
   if (h->lat)
@@ -264,19 +264,19 @@ int precond_apply(pfc_handle *h, const double *in, double *out, const Ctl *ctl)
   double *x = xa, *xn = xb;
   for (int i = 1; i < h->sweeps; ++i)
     {
-      PFC_TRY(halo_exchange_scalar(h, x));
+      PFC_TRY(halo_exchange_scalar(h, x, ctl));
       run_kmv(h, S, nb, nullptr, 0.0, x, 1.0, t1, nullptr, ctl);
-      PFC_TRY(halo_exchange_scalar(h, t1));
+      PFC_TRY(halo_exchange_scalar(h, t1, ctl));
       run_kmv(h, S, nb, nullptr, 0.0, t1, 1.0, t2, nullptr, ctl);
-      PFC_TRY(halo_exchange_scalar(h, t2));
+      PFC_TRY(halo_exchange_scalar(h, t2, ctl));
       run_bcd<1>(h, S, nb, x, t1, t2, 1.0, -1.0, 1.0, rhs, h->d_dinvB.p, d, h->d_cheb.p + 2 * i, xn, ctl);
       std::swap(x, xn);
       h->launches += 3;
     }
   // back substitution; psi -> out[0], chi -> out[1], phi -> out[2]
-  PFC_TRY(halo_exchange_scalar(h, x));
+  PFC_TRY(halo_exchange_scalar(h, x, ctl));
   run_kmv(h, S, nb, r1, 1.0, x, -1.0, chi, out + Np, ctl);              // chi = M_L^-1 (r1 - K psi)
-  PFC_TRY(halo_exchange_scalar(h, chi));
+  PFC_TRY(halo_exchange_scalar(h, chi, ctl));
   run_kmv(h, S, nb, r2, 1.0, chi, -1.0, out + 2 * Np, nullptr, ctl);    // phi = M_L^-1 (r2 - K chi)
   vec_mul_kernel<<<g, 256, 0, s>>>(out, nullptr, 1.0, nullptr, x, nullptr, Np, ctl);
   h->launches += 3;

@@ -163,7 +163,7 @@ static int launch_mf(pfc_handle *h, const double *x, double *y, const Ctl *ctl)
 // y = J x with the halo of x refreshed first (multi-rank)
 static int apply_operator(pfc_handle *h, double *x, double *y, const Ctl *ctl)
 {
-  PFC_TRY(halo_exchange(h, x));
+  PFC_TRY(halo_exchange(h, x, ctl));
   if (h->lat)
     {
       LatOp op = lat_op(h);
@@ -233,7 +233,7 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass)
     PFC_TRY(apply_operator(h, h->d_x.p, V, ctl));
   residual_kernel<<<grid, kVecThreads, 0, s>>>(V, h->d_rhs.p, n2, first_cycle ? 0 : 1, partial, &g->nrm2[0], cnt, ctl);
   h->launches++;
-  PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1));
+  PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1, ctl));
   cycle_begin_kernel<<<1, 1, 0, s>>>(g, ctl);
   scale_kernel<<<grid, kVecThreads, 0, s>>>(V, n2, ctl);
   h->launches += 2;
@@ -250,15 +250,15 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass)
       else
         PFC_TRY(apply_operator(h, V + (int64_t)inner * st, w, ctl)); // A.vmult
       g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots0, cnt, ctl, 0);
-      PFC_TRY(allreduce_sum(h, g->dots0, dim + 1));
+      PFC_TRY(allreduce_sum(h, g->dots0, dim + 1, ctl));
       g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots0, partial, &g->nrm2[0], cnt, ctl, 0);
-      PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1));
+      PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1, ctl));
       if (two_pass)
         {
           g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots1, cnt, ctl, 1);
-          PFC_TRY(allreduce_sum(h, g->dots1, dim + 1));
+          PFC_TRY(allreduce_sum(h, g->dots1, dim + 1, ctl));
           g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots1, partial, &g->nrm2[1], cnt, ctl, 1);
-          PFC_TRY(allreduce_sum(h, &g->nrm2[1], 1));
+          PFC_TRY(allreduce_sum(h, &g->nrm2[1], 1, ctl));
           h->launches += 2;
         }
       givens_kernel<<<1, 1, 0, s>>>(g, ctl, inner, two_pass ? 1 : 0);
