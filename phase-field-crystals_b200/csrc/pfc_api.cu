@@ -127,9 +127,10 @@ extern "C" void pfc_destroy(pfc_handle *h)
   cudaSetDevice(h->device);
   if (h->stream)
     cudaStreamSynchronize(h->stream);
-  for (auto &g : h->cycle_graph)
-    if (g)
-      cudaGraphExecDestroy(g);
+  for (auto &kv : h->cycle_graphs)
+    if (kv.second.exec)
+      cudaGraphExecDestroy(kv.second.exec);
+  h->cycle_graphs.clear();
   comm_destroy(h);
   for (auto &ev : h->ev)
     if (ev)
@@ -240,6 +241,8 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
   }
   PFC_CUDA(h, h->d_io.alloc(P.n_dofs));
   PFC_CUDA(h, h->d_ctl.alloc(1));
+  PFC_CUDA(h, h->d_ctl_end.alloc(1));
+  PFC_CUDA(h, cudaMemsetAsync(h->d_ctl_end.p, 0, sizeof(Ctl), s));
   PFC_CUDA(h, h->d_small.alloc(1));
   PFC_CUDA(h, h->d_partial.alloc((size_t)kPartialStride * 4096));
   PFC_CUDA(h, h->d_counter.alloc(4));
@@ -264,12 +267,12 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
       if (rc != PFC_OK)
         return rc;
     }
-  for (auto &g : h->cycle_graph)
-    if (g)
-      {
-        cudaGraphExecDestroy(g);
-        g = nullptr;
-      }
+  for (auto &kv : h->cycle_graphs)
+    if (kv.second.exec)
+      cudaGraphExecDestroy(kv.second.exec);
+  h->cycle_graphs.clear();
+  for (int &v : h->pred_iters)
+    v = 0;
   h->is_setup = true;
   // iterate-independent blocks M and K, once (they are re-assembled every Newton iteration
   // upstream, mpi.cpp:435-443, with identical values); the lattice path stores no matrix at all

@@ -4,6 +4,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -90,8 +91,17 @@ struct pfc_handle
   pfc::DevBuf<unsigned int> d_counter;
   pfc::Ctl *h_ctl = nullptr; // pinned
   double *h_scalar = nullptr; // pinned [4]
-  cudaGraphExec_t cycle_graph[4] = {nullptr, nullptr, nullptr, nullptr}; // [first cycle (x = 0), later] x [one, two GS passes]
-  int64_t graph_launches[4] = {0, 0, 0, 0};
+  // restart-cycle graphs, keyed by (first cycle (x = 0) | later, one | two GS passes, iterations [i0, i1)): a cycle is
+  // launched as [0, L) with L predicted from the previous time step and, if it has not converged by then, [L, restart)
+  struct CycleGraph
+  {
+    cudaGraphExec_t exec = nullptr;
+    int64_t launches = 0;
+  };
+  std::map<int, CycleGraph> cycle_graphs;
+  pfc::DevBuf<pfc::Ctl> d_ctl_end;  // gate of the cycle's end part: state 0 = run (converged, failed or restart length reached)
+  int pred_iters[8] = {0, 0, 0, 0, 0, 0, 0, 0}; // iterations of the k-th solve of the previous time step
+  int solve_index = 0;
 
   // multi-GPU
   ncclComm *comm = nullptr;

@@ -250,9 +250,18 @@ static __global__ void cycle_begin_kernel(GmresSmall *g, Ctl *ctl)
   ctl->inv_norm = rho != 0.0 ? 1.0 / rho : 1.0;
 }
 
-// end of a cycle: back substitution H y = gamma (H1.backward), dim = ctl->dim
-static __global__ void backsolve_kernel(GmresSmall *g, Ctl *ctl)
+// gate of the end part when a cycle is enqueued in two pieces: the end runs (gate->state = 0) once the solve has
+// stopped or the restart length is reached, otherwise the continuation graph follows and runs it
+static __global__ void end_gate_kernel(const Ctl *ctl, Ctl *gate, int restart)
 {
+  gate->state = (ctl->state != 0 || ctl->dim >= restart) ? 0 : 1;
+}
+
+// end of a cycle: back substitution H y = gamma (H1.backward), dim = ctl->dim
+static __global__ void backsolve_kernel(GmresSmall *g, Ctl *ctl, const Ctl *gate)
+{
+  if (gate->state != 0)
+    return;
   const int dim = ctl->dim;
   for (int i = dim - 1; i >= 0; --i)
     {
@@ -266,10 +275,10 @@ static __global__ void backsolve_kernel(GmresSmall *g, Ctl *ctl)
 // x += sum_{i < dim} y_i V_i ; dim read from the device; consumes the cycle (dim := 0)
 static __global__ void __launch_bounds__(kVecThreads) xupdate_kernel(const double *__restrict__ V, int64_t stride,
                                                               double *__restrict__ x, int64_t n2,
-                                                              const GmresSmall *g, const Ctl *ctl)
+                                                              const GmresSmall *g, const Ctl *ctl, const Ctl *gate)
 {
   const int dim = ctl->dim;
-  if (dim <= 0)
+  if (dim <= 0 || gate->state != 0)
     return;
   __shared__ double s_y[kMaxBasis];
   if (threadIdx.x < dim)
@@ -304,8 +313,10 @@ static __global__ void distribute_kernel(double *v, const int32_t *slave, const 
 }
 
 // Psi_n += dPsi_n (mpi.cpp:487-491) over the whole local vector
-static __global__ void axpy1_kernel(double *__restrict__ y, const double *__restrict__ x, int64_t n)
+static __global__ void axpy1_kernel(double *__restrict__ y, const double *__restrict__ x, int64_t n, const Ctl *ctl = nullptr)
 {
+  if (ctl && ctl->state != 0)
+    return;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     y[i] += x[i];
 }

@@ -212,8 +212,9 @@ static void ensure_tab()
     }
 }
 
-// ---- one restart cycle, enqueued on the stream (captured into a CUDA graph when enabled) -----------
-static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass)
+// ---- one restart cycle, or the piece [i0, i1) of its iterations, enqueued on the stream (captured into a CUDA
+//      graph when enabled).  i0 == 0 starts the cycle; every piece ends with the gated end part -----------------
+static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0, int i1)
 {
   ensure_tab();
   const Plan &P = h->plan;
@@ -221,6 +222,7 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass)
   const int64_t n2 = 3 * P.Np / 2;
   const int grid = vec_grid(h, n2);
   Ctl *ctl = h->d_ctl.p;
+  Ctl *gate = h->d_ctl_end.p;
   GmresSmall *g = h->d_small.p;
   double *V = h->d_V.p;
   const int64_t st = h->stride;
@@ -228,17 +230,20 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass)
   unsigned int *cnt = h->d_counter.p;
   const bool precond = h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR;
 
-  // v0 = b - A x ; rho = ||v0|| ; check ; v0 /= rho          ([dealii-ext] start of the outer loop)
-  if (!first_cycle)
-    PFC_TRY(apply_operator(h, h->d_x.p, V, ctl));
-  residual_kernel<<<grid, kVecThreads, 0, s>>>(V, h->d_rhs.p, n2, first_cycle ? 0 : 1, partial, &g->nrm2[0], cnt, ctl);
-  h->launches++;
-  PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1, ctl));
-  cycle_begin_kernel<<<1, 1, 0, s>>>(g, ctl);
-  scale_kernel<<<grid, kVecThreads, 0, s>>>(V, n2, ctl);
-  h->launches += 2;
+  if (i0 == 0)
+    {
+      // v0 = b - A x ; rho = ||v0|| ; check ; v0 /= rho          ([dealii-ext] start of the outer loop)
+      if (!first_cycle)
+        PFC_TRY(apply_operator(h, h->d_x.p, V, ctl));
+      residual_kernel<<<grid, kVecThreads, 0, s>>>(V, h->d_rhs.p, n2, first_cycle ? 0 : 1, partial, &g->nrm2[0], cnt, ctl);
+      h->launches++;
+      PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1, ctl));
+      cycle_begin_kernel<<<1, 1, 0, s>>>(g, ctl);
+      scale_kernel<<<grid, kVecThreads, 0, s>>>(V, n2, ctl);
+      h->launches += 2;
+    }
 
-  for (int inner = 0; inner < h->restart; ++inner)
+  for (int inner = i0; inner < i1; ++inner)
     {
       const int dim = inner + 1;
       double *w = V + (int64_t)dim * st;
@@ -265,35 +270,37 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass)
       scale_kernel<<<grid, kVecThreads, 0, s>>>(w, n2, ctl);
       h->launches += 5;
     }
-  backsolve_kernel<<<1, 1, 0, s>>>(g, ctl);
+  // end part: runs when the solve has stopped or the restart length is reached, else the continuation piece follows
+  end_gate_kernel<<<1, 1, 0, s>>>(ctl, gate, h->restart);
+  backsolve_kernel<<<1, 1, 0, s>>>(g, ctl, gate);
   if (precond)
     { // x += P^-1 (V y)
-      PFC_CUDA(h, cudaMemsetAsync(h->d_u.p, 0, h->d_u.n * sizeof(double), s));
-      xupdate_kernel<<<grid, kVecThreads, 0, s>>>(V, st, h->d_u.p, n2, g, ctl);
-      PFC_TRY(precond_apply(h, h->d_u.p, h->d_z.p, nullptr));
-      axpy1_kernel<<<grid, kVecThreads, 0, s>>>(h->d_x.p, h->d_z.p, 3 * P.Np);
+      PFC_CUDA(h, cudaMemsetAsync(h->d_u.p, 0, 3 * P.Np * sizeof(double), s));
+      xupdate_kernel<<<grid, kVecThreads, 0, s>>>(V, st, h->d_u.p, n2, g, ctl, gate);
+      PFC_TRY(precond_apply(h, h->d_u.p, h->d_z.p, gate));
+      axpy1_kernel<<<grid, kVecThreads, 0, s>>>(h->d_x.p, h->d_z.p, 3 * P.Np, gate);
       h->launches++;
     }
   else
-    xupdate_kernel<<<grid, kVecThreads, 0, s>>>(V, st, h->d_x.p, n2, g, ctl);
-  h->launches += 2;
+    xupdate_kernel<<<grid, kVecThreads, 0, s>>>(V, st, h->d_x.p, n2, g, ctl, gate);
+  h->launches += 3;
   PFC_CUDA(h, cudaMemcpyAsync(h->h_ctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s));
   PFC_CUDA(h, cudaGetLastError());
   return PFC_OK;
 }
 
-static int run_cycle(pfc_handle *h, bool first_cycle, bool two_pass)
+static int run_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0, int i1)
 {
-  const int gi = (first_cycle ? 0 : 1) + (two_pass ? 2 : 0);
   if (!h->prm.use_cuda_graph)
-    return enqueue_cycle(h, first_cycle, two_pass);
-  if (!h->cycle_graph[gi])
+    return enqueue_cycle(h, first_cycle, two_pass, i0, i1);
+  const int key = ((i0 * 64 + i1) * 2 + (first_cycle ? 0 : 1)) * 2 + (two_pass ? 1 : 0);
+  pfc_handle::CycleGraph &cg = h->cycle_graphs[key];
+  if (!cg.exec)
     {
       const int64_t before = h->launches;
       cudaGraph_t graph = nullptr;
       PFC_CUDA(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-      comm_p2p_unknown_predecessor(h);
-      const int rc = enqueue_cycle(h, first_cycle, two_pass);
+      const int rc = enqueue_cycle(h, first_cycle, two_pass, i0, i1);
       cudaError_t e = cudaStreamEndCapture(h->stream, &graph);
       if (rc != PFC_OK)
         {
@@ -302,14 +309,13 @@ static int run_cycle(pfc_handle *h, bool first_cycle, bool two_pass)
           return rc;
         }
       PFC_CUDA(h, e);
-      PFC_CUDA(h, cudaGraphInstantiate(&h->cycle_graph[gi], graph, 0));
+      PFC_CUDA(h, cudaGraphInstantiate(&cg.exec, graph, 0));
       cudaGraphDestroy(graph);
-      h->graph_launches[gi] = h->launches - before; // kernel nodes recorded in the graph
-      h->launches = before;                          // capture launched nothing
+      cg.launches = h->launches - before; // kernel nodes recorded in the graph
+      h->launches = before;               // capture launched nothing
     }
-  PFC_CUDA(h, cudaGraphLaunch(h->cycle_graph[gi], h->stream));
-  comm_p2p_unknown_predecessor(h);
-  h->launches += h->graph_launches[gi];
+  PFC_CUDA(h, cudaGraphLaunch(cg.exec, h->stream));
+  h->launches += cg.launches;
   return PFC_OK;
 }
 
@@ -324,15 +330,27 @@ static int gmres_solve(pfc_handle *h, int64_t *iters, double *final_res)
   c0.max_iters = h->prm.gmres_max_iters > 0 ? h->prm.gmres_max_iters : P.n_dofs;
   *h->h_ctl = c0;
   PFC_CUDA(h, cudaMemcpyAsync(h->d_ctl.p, h->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, s));
-  // owned part only: the ghost tail is written by the neighbours (p2p) and refreshed before every use
+  // owned part only: the ghost tail is refreshed before every use
   PFC_CUDA(h, cudaMemsetAsync(h->d_x.p, 0, 3 * P.Np * sizeof(double), s));
   PFC_CUDA(h, cudaStreamSynchronize(s)); // h_ctl is reused as the read-back buffer
   bool first = true, two_pass = h->prm.orthogonalization == PFC_ORTHO_CGS2;
+  // first piece of a cycle: as many iterations as the same solve of the previous time step needed (+ slack, multiple
+  // of 4 so that few graphs exist); the kernels of a longer graph would all be launched just to skip themselves
+  const int slot = std::min(h->solve_index, 7);
+  const int pred = h->pred_iters[slot];
   for (;;)
     {
-      PFC_TRY(run_cycle(h, first, two_pass));
-      first = false;
+      int L = h->restart;
+      if (first && pred > 0 && h->prm.use_cuda_graph)
+        L = std::min(h->restart, (pred + 1 + 3) / 4 * 4);
+      PFC_TRY(run_cycle(h, first, two_pass, 0, L));
       PFC_CUDA(h, cudaStreamSynchronize(s));
+      if (h->h_ctl->state == 0 && h->h_ctl->dim == L && L < h->restart)
+        { // not there yet: the rest of the cycle
+          PFC_TRY(run_cycle(h, first, two_pass, L, h->restart));
+          PFC_CUDA(h, cudaStreamSynchronize(s));
+        }
+      first = false;
       if (h->h_ctl->state == 3)
         { // Kelley test tripped: go on with two Gram-Schmidt passes per iteration (sticky)
           two_pass = true;
@@ -344,6 +362,8 @@ static int gmres_solve(pfc_handle *h, int64_t *iters, double *final_res)
       if (h->h_ctl->state != 0)
         break;
     }
+  h->pred_iters[slot] = (int)std::min<long long>(h->h_ctl->iters, h->restart);
+  h->solve_index++;
   if (iters)
     *iters = h->h_ctl->iters;
   if (final_res)
@@ -435,6 +455,7 @@ extern "C" int pfc_step(pfc_handle *h, pfc_step_stats *st)
     st = &local;
   std::memset(st, 0, sizeof(*st));
   const int64_t launches0 = h->launches;
+  h->solve_index = 0;
   cudaStream_t s = h->stream;
   PFC_CUDA(h, cudaEventRecord(h->ev[0], s));
   int status = PFC_WARN_NEWTON_MAX_ITERS;
