@@ -11,6 +11,7 @@
 
 #include "pfc_comm.h"
 #include "pfc_handle.h"
+#include "pfc_p2p.cuh"
 
 namespace
 {
@@ -335,16 +336,6 @@ int halo_exchange_scalar(pfc_handle *h, double *v, const Ctl *ctl)
 // same sequence of collective kernels.  A rank cannot send exchange n+2 before it has received n+1, which
 // its neighbour sends after it has consumed n, so two buffer halves (epoch parity) are enough.
 // =====================================================================================================
-constexpr int kMaxRanksP2P = 8;
-constexpr int kArSlot = 72;
-
-struct P2PSync
-{ // one per rank, peer-visible
-  uint4 ar_ll[2][kMaxRanksP2P][kArSlot]; // [epoch parity][source rank][value]
-  unsigned long long halo_epoch, ar_epoch; // local
-  unsigned int block_counter;
-};
-
 struct P2PState
 {
   int R = 0, me = 0;
@@ -365,35 +356,6 @@ struct P2PHaloArgs
   int64_t my_half, n_ghost;
 };
 
-struct P2PArArgs
-{
-  P2PSync *sync[kMaxRanksP2P];
-  int R, me;
-};
-
-__device__ __forceinline__ unsigned int ll_tag(unsigned long long e) { return (unsigned int)(e & 0x7fffffffu) | 0x80000000u; }
-__device__ __forceinline__ void ll_store(uint4 *p, double v, unsigned int tag)
-{
-  const unsigned long long b = (unsigned long long)__double_as_longlong(v);
-  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"((unsigned int)b), "r"(tag),
-               "r"((unsigned int)(b >> 32)), "r"(tag)
-               : "memory");
-}
-// bounded wait: a peer that never arrives must not hang the GPU (trap -> CUDA error on the host)
-__device__ __forceinline__ double ll_wait(const uint4 *p, unsigned int tag)
-{
-  unsigned int lo, t0, hi, t1;
-  const long long c0 = clock64();
-  for (;;)
-    {
-      asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(lo), "=r"(t0), "=r"(hi), "=r"(t1) : "l"(p) : "memory");
-      if (t0 == tag && t1 == tag)
-        break;
-      if (clock64() - c0 > 20000000000ll)
-        __trap();
-    }
-  return __longlong_as_double((long long)(((unsigned long long)hi << 32) | lo));
-}
 
 // grid is capped (all CTAs resident): every thread first stores all its values, then polls
 template <int NC>
@@ -441,40 +403,32 @@ static __global__ void __launch_bounds__(256) p2p_halo_kernel(P2PHaloArgs H, dou
     }
 }
 
-static __global__ void __launch_bounds__(128) p2p_allreduce_kernel(P2PArArgs A, double *dev, int n, P2PSync *sl,
-                                                                    const Ctl *ctl)
+static __global__ void __launch_bounds__(128) p2p_allreduce_kernel(ArDev A, double *dev, int n, const Ctl *ctl)
 {
   if (ctl && ctl->state != 0)
     return;
-  const unsigned long long e = sl->ar_epoch + 1;
-  const unsigned int tag = ll_tag(e);
-  const int b = (int)(e & 1), t = threadIdx.x;
-  if (t < n)
+  ar_block_allreduce(A, dev, n);
+}
+
+ArDev comm_ar_endpoint(const pfc_handle *h)
+{
+  ArDev A;
+  std::memset(&A, 0, sizeof(A));
+  if (h->p2p && h->p2p_state)
     {
-      const double val = dev[t];
-      for (int q = 0; q < A.R; ++q)
-        ll_store(&A.sync[q]->ar_ll[b][A.me][t], val, tag);
-      double s = 0;
-      for (int src = 0; src < A.R; ++src)
-        s += ll_wait(&sl->ar_ll[b][src][t], tag);
-      dev[t] = s;
+      for (int q = 0; q < kMaxRanksP2P; ++q)
+        A.sync[q] = h->p2p_state->sync[q];
+      A.R = h->p2p_state->R;
+      A.me = h->p2p_state->me;
     }
-  __syncthreads();
-  if (t == 0)
-    sl->ar_epoch = e;
+  return A;
 }
 
 static int p2p_allreduce(pfc_handle *h, double *dev, size_t n, const Ctl *ctl)
 {
-  P2PState &S = *h->p2p_state;
   if (n > (size_t)kArSlot)
     return h->fail(PFC_ERR_NCCL, "p2p all-reduce of %zu values (max %d)", n, kArSlot);
-  P2PArArgs A;
-  for (int q = 0; q < kMaxRanksP2P; ++q)
-    A.sync[q] = S.sync[q];
-  A.R = S.R;
-  A.me = S.me;
-  p2p_allreduce_kernel<<<1, 128, 0, h->stream>>>(A, dev, (int)n, S.sync[S.me], ctl);
+  p2p_allreduce_kernel<<<1, 128, 0, h->stream>>>(comm_ar_endpoint(h), dev, (int)n, ctl);
   h->launches++;
   return PFC_OK;
 }

@@ -26,5 +26,7 @@ namespace pfc
 struct Ctl;
 int comm_p2p_setup(pfc_handle *h);     // after the arena exists; collective; h->p2p = false -> NCCL stays in charge
 void comm_p2p_destroy(pfc_handle *h);
+struct ArDev;
+ArDev comm_ar_endpoint(const pfc_handle *h); // R == 0 unless the peer-memory path is active (pfc_p2p.cuh)
 void comm_p2p_unknown_predecessor(pfc_handle *h); // before a graph capture / launch: force a flag-only round first
 } // namespace pfc

@@ -5,6 +5,7 @@
 // test, Givens QR of the Hessenberg matrix, stop on |gamma_dim| <= tol.
 #pragma once
 #include "pfc_kernels.cuh"
+#include "pfc_p2p.cuh"
 
 namespace pfc
 {
@@ -22,9 +23,11 @@ __device__ __forceinline__ double warp_sum(double v)
 
 // Deterministic grid reduction of NV values per block: per-warp shuffle, per-block shared memory,
 // per-grid "last block sums the partials in block order".  out[i] = sum over blocks.
+// ar.R > 0: the last block also all-reduces the NV results over the ranks (peer-memory slots, rank order), so no
+// separate collective kernel follows.
 template <int NV>
 __device__ __forceinline__ void grid_reduce(double (&acc)[NV], double *partial, double *out,
-                                            unsigned int *counter)
+                                            unsigned int *counter, const ArDev &ar)
 {
   __shared__ double s_red[kVecThreads / 32][NV];
   __shared__ bool s_last;
@@ -65,6 +68,11 @@ __device__ __forceinline__ void grid_reduce(double (&acc)[NV], double *partial, 
         }
       if (threadIdx.x == 0)
         *counter = 0;
+      if (ar.R > 1)
+        {
+          __syncthreads();
+          ar_block_allreduce(ar, out, NV);
+        }
     }
 }
 
@@ -74,7 +82,7 @@ template <int DIM>
 static __global__ void __launch_bounds__(kVecThreads) multidot_kernel(const double *__restrict__ V, int64_t stride,
                                                                const double *__restrict__ w, int64_t n2,
                                                                double *partial, double *out,
-                                                               unsigned int *counter, const Ctl *ctl, int pass)
+                                                               unsigned int *counter, const Ctl *ctl, int pass, ArDev ar)
 {
   (void)pass;
   if (ctl && ctl->state != 0)
@@ -95,7 +103,7 @@ static __global__ void __launch_bounds__(kVecThreads) multidot_kernel(const doub
           acc[i] += v.x * wv.x + v.y * wv.y;
         }
     }
-  grid_reduce<DIM + 1>(acc, partial, out, counter);
+  grid_reduce<DIM + 1>(acc, partial, out, counter, ar);
 }
 
 // w -= sum_i h_i V_i ; out[0] = ||w||^2 after the update.  The last block also applies the
@@ -105,7 +113,7 @@ static __global__ void __launch_bounds__(kVecThreads) multiaxpy_kernel(const dou
                                                                 double *__restrict__ w, int64_t n2,
                                                                 const double *__restrict__ h, double *partial,
                                                                 double *out, unsigned int *counter, Ctl *ctl,
-                                                                int pass)
+                                                                int pass, ArDev ar)
 {
   (void)pass;
   if (ctl->state != 0)
@@ -129,7 +137,7 @@ static __global__ void __launch_bounds__(kVecThreads) multiaxpy_kernel(const dou
       w2[idx] = wv;
       acc[0] += wv.x * wv.x + wv.y * wv.y;
     }
-  grid_reduce<1>(acc, partial, out, counter);
+  grid_reduce<1>(acc, partial, out, counter, ar);
 }
 
 // per-solve small state on the device
@@ -212,7 +220,7 @@ static __global__ void __launch_bounds__(kVecThreads) scale_kernel(double *__res
 // restart: v0 = b - A x (A x is in v0 on entry, or use_ax = 0 when x = 0), out[0] = ||v0||^2
 static __global__ void __launch_bounds__(kVecThreads) residual_kernel(double *__restrict__ v0, const double *__restrict__ b,
                                                                int64_t n2, int use_ax, double *partial, double *out,
-                                                               unsigned int *counter, const Ctl *ctl)
+                                                               unsigned int *counter, const Ctl *ctl, ArDev ar)
 {
   if (ctl->state != 0)
     return;
@@ -231,7 +239,7 @@ static __global__ void __launch_bounds__(kVecThreads) residual_kernel(double *__
       v2[idx] = r;
       acc[0] += r.x * r.x + r.y * r.y;
     }
-  grid_reduce<1>(acc, partial, out, counter);
+  grid_reduce<1>(acc, partial, out, counter, ar);
 }
 
 // start of a restart cycle: rho = ||b - A x||, check, gamma_0 = rho

@@ -140,7 +140,7 @@ static int scalar_norm(pfc_handle *h, const double *v, double *out)
   const int64_t n2 = h->plan.Np / 2;
   GmresSmall *g = h->d_small.p;
   multidot_kernel<0><<<vgrid(h, n2), kVecThreads, 0, h->stream>>>(nullptr, 0, v, n2, h->d_partial.p, &g->nrm2[0],
-                                                                  h->d_counter.p, nullptr, 0);
+                                                                  h->d_counter.p, nullptr, 0, ArDev{});
   h->launches++;
   PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1));
   PFC_CUDA(h, cudaMemcpyAsync(h->h_scalar, &g->nrm2[0], sizeof(double), cudaMemcpyDeviceToHost, h->stream));

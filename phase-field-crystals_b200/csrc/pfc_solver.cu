@@ -178,8 +178,8 @@ static int apply_operator(pfc_handle *h, double *x, double *y, const Ctl *ctl)
 }
 
 // ---- template dispatch over the Krylov dimension ---------------------------------------------------
-using DotFn = void (*)(const double *, int64_t, const double *, int64_t, double *, double *, unsigned int *, const Ctl *, int);
-using AxpyFn = void (*)(const double *, int64_t, double *, int64_t, const double *, double *, double *, unsigned int *, Ctl *, int);
+using DotFn = void (*)(const double *, int64_t, const double *, int64_t, double *, double *, unsigned int *, const Ctl *, int, ArDev);
+using AxpyFn = void (*)(const double *, int64_t, double *, int64_t, const double *, double *, double *, unsigned int *, Ctl *, int, ArDev);
 constexpr int kMaxDim = 32;
 template <int D>
 struct Tab
@@ -229,15 +229,19 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0,
   double *partial = h->d_partial.p;
   unsigned int *cnt = h->d_counter.p;
   const bool precond = h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR;
+  // peer-memory path: the reduction kernels all-reduce their results in their last block (no collective kernel)
+  const ArDev ar = comm_ar_endpoint(h);
+  const bool fused = ar.R > 1;
 
   if (i0 == 0)
     {
       // v0 = b - A x ; rho = ||v0|| ; check ; v0 /= rho          ([dealii-ext] start of the outer loop)
       if (!first_cycle)
         PFC_TRY(apply_operator(h, h->d_x.p, V, ctl));
-      residual_kernel<<<grid, kVecThreads, 0, s>>>(V, h->d_rhs.p, n2, first_cycle ? 0 : 1, partial, &g->nrm2[0], cnt, ctl);
+      residual_kernel<<<grid, kVecThreads, 0, s>>>(V, h->d_rhs.p, n2, first_cycle ? 0 : 1, partial, &g->nrm2[0], cnt, ctl, ar);
       h->launches++;
-      PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1, ctl));
+      if (!fused)
+        PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1, ctl));
       cycle_begin_kernel<<<1, 1, 0, s>>>(g, ctl);
       scale_kernel<<<grid, kVecThreads, 0, s>>>(V, n2, ctl);
       h->launches += 2;
@@ -254,16 +258,20 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0,
         }
       else
         PFC_TRY(apply_operator(h, V + (int64_t)inner * st, w, ctl)); // A.vmult
-      g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots0, cnt, ctl, 0);
-      PFC_TRY(allreduce_sum(h, g->dots0, dim + 1, ctl));
-      g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots0, partial, &g->nrm2[0], cnt, ctl, 0);
-      PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1, ctl));
+      g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots0, cnt, ctl, 0, ar);
+      if (!fused)
+        PFC_TRY(allreduce_sum(h, g->dots0, dim + 1, ctl));
+      g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots0, partial, &g->nrm2[0], cnt, ctl, 0, ar);
+      if (!fused)
+        PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1, ctl));
       if (two_pass)
         {
-          g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots1, cnt, ctl, 1);
-          PFC_TRY(allreduce_sum(h, g->dots1, dim + 1, ctl));
-          g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots1, partial, &g->nrm2[1], cnt, ctl, 1);
-          PFC_TRY(allreduce_sum(h, &g->nrm2[1], 1, ctl));
+          g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots1, cnt, ctl, 1, ar);
+          if (!fused)
+            PFC_TRY(allreduce_sum(h, g->dots1, dim + 1, ctl));
+          g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots1, partial, &g->nrm2[1], cnt, ctl, 1, ar);
+          if (!fused)
+            PFC_TRY(allreduce_sum(h, &g->nrm2[1], 1, ctl));
           h->launches += 2;
         }
       givens_kernel<<<1, 1, 0, s>>>(g, ctl, inner, two_pass ? 1 : 0);
@@ -397,7 +405,7 @@ static int residual_norm_async(pfc_handle *h)
   const int64_t n2 = 3 * h->plan.Np / 2;
   GmresSmall *g = h->d_small.p;
   g_dot[0]<<<vec_grid(h, n2), kVecThreads, 0, h->stream>>>(nullptr, 0, h->d_rhs.p, n2, h->d_partial.p, &g->nrm2[0],
-                                                            h->d_counter.p, nullptr, 0);
+                                                            h->d_counter.p, nullptr, 0, ArDev{});
   h->launches++;
   PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1));
   PFC_CUDA(h, cudaMemcpyAsync(h->h_scalar, &g->nrm2[0], sizeof(double), cudaMemcpyDeviceToHost, h->stream));
@@ -650,15 +658,15 @@ extern "C" int pfc_time_krylov(pfc_handle *h, int32_t dim, int32_t reps, double 
     {
       for (int i = 0; i < 2; ++i) // warm-up
         if (k == 0)
-          g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0);
+          g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0, ArDev{});
         else
-          g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0);
+          g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
       PFC_CUDA(h, cudaEventRecord(h->ev[0], s));
       for (int i = 0; i < reps; ++i)
         if (k == 0)
-          g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0);
+          g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0, ArDev{});
         else
-          g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0);
+          g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
       h->launches += reps + 2;
       PFC_CUDA(h, cudaEventRecord(h->ev[1], s));
       PFC_CUDA(h, cudaStreamSynchronize(s));
