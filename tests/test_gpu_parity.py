@@ -264,3 +264,31 @@ def test_lattice_k_stencil_matches_cell_quadrature(built, degree, n_refines):
     print("K stencil vs cells:", err)
     assert 0.0 < err <= 1e-13
     s.close()
+
+
+@pytest.mark.parametrize("degree,n_refines,kw", [(1, 5, {}), (1, 5, {"operator_kind": 1, "preconditioner": 1}),
+                                                 (2, 4, {"operator_kind": 1, "preconditioner": 1})])
+def test_hundred_steps_within_1e7(built, degree, n_refines, kw):
+    """north_star: psi relative L2 <= 1e-7 after 100 steps (<= 1e-9 per step is checked by the step tests).
+    A 4a x 4a box keeps the lattice resolved at sizes the oracle finishes 100 steps of in about a minute
+    (on the 12a x 10a box of the other tests 2^4 cells are too coarse: the oracle itself blows up after ~30 steps)."""
+    import oracle as O
+    p1, p2 = (-2 * A, -2 * A), (2 * A, 2 * A)
+    om = O.Mesh(degree, n_refines, p1, p2)
+    st = built.StandIn(degree, n_refines, p1, p2)
+    Psi = st.hexagonal_lattice(built.default_A0(PSI0, EPS), PSI0, [[A, 0], [-A, 0]], BURG)
+    s = built.Solver(degree=degree, theta=1.0, **kw)
+    s.setup(st)
+    s.set_state(Psi, Psi)
+    Pn, Pn1 = Psi.copy(), Psi.copy()
+    worst = 0.0
+    for step in range(100):
+        g = s.step()
+        o = om.newton_step(Pn, Pn1, DT, 1.0, EPS)
+        assert g["status"] == 0 and o["status"] == 0
+        if step % 10 == 9:
+            worst = max(worst, _rel(s.get_state()[:om.N], Pn[:om.N]))
+    got = s.get_state()
+    print(f"100 steps Q{degree} 2^{n_refines} {kw}: rel L2 psi {_rel(got[:om.N], Pn[:om.N]):.2e} (worst at a multiple of 10: {worst:.2e})")
+    assert _rel(got[:om.N], Pn[:om.N]) <= 1e-7 and _rel(got, Pn) <= 1e-7
+    s.close()
