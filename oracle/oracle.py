@@ -71,6 +71,8 @@ def lib():
                                       C.c_double, C.c_int, C.c_double, C.c_int, dp,
                                       C.POINTER(C.c_int64), C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.orc_distribute.argtypes = [C.POINTER(_Mesh), dp]
+        L.orc_stress.restype = C.c_int
+        L.orc_stress.argtypes = [C.POINTER(_Mesh), dp, C.c_double, C.c_double, dp, C.POINTER(C.c_int64), dp]
         L.orc_max_threads.restype = C.c_int
         L.orc_set_threads.argtypes = [C.c_int]
         _lib = L
@@ -167,6 +169,15 @@ class Mesh:
                                    C.byref(status))
         return {"gmres_iters": gm[:ns].tolist(), "residuals": res[:nasm.value].tolist(),
                 "n_assemblies": nasm.value, "status": status.value}
+
+    def stress(self, Psi, eps, tol=1e-10):
+        """StressCalculatorMPI::calculate_stress (stress.cpp:345-352): [4][N] nodal stress, c = a*2 + b."""
+        out = np.zeros((4, self.N))
+        rhs = np.zeros((4, self.N))
+        its = np.zeros(4, dtype=np.int64)
+        st = lib().orc_stress(self._p, _dp(np.ascontiguousarray(Psi)), eps, tol, _dp(out),
+                              its.ctypes.data_as(C.POINTER(C.c_int64)), _dp(rhs))
+        return {"stress": out, "rhs": rhs, "cg_iters": its.tolist(), "status": st}
 
     def distribute(self, v):
         lib().orc_distribute(self._p, _dp(v))

@@ -877,3 +877,199 @@ int orc_newton_step(const orc_mesh *m, double *Psi_n, double *Psi_n1, double dt,
   free(dPsi);
   return n_solves;
 }
+
+/* ------------------------------------------------------------------------------------------
+ * Stress projection.  stress.cpp = src/stress_tools/stress_calculator_mpi.cpp.
+ * The reference's FESystem(FE_Q(degree), dim*dim) shares the scalar FE_Q(degree) node set with
+ * the (psi, chi, phi) system, so component c = a*dim + b of the stress lives on scalar node t
+ * at stress[c*N + t] (dof numbering of the psi block; the reference's own block-wise
+ * renumbering, stress.cpp:46-58, is a permutation of this).
+ * ------------------------------------------------------------------------------------------ */
+static void scalar_cell_nodes(const orc_mesh *m, int64_t cell, int32_t *node)
+{
+  /* node[a] = global dof of the psi component carried by scalar shape a (dof = 0*N + t) */
+  const int32_t *dofs = m->cell_dofs + cell * m->dofs_per_cell;
+  for (int k = 0; k < m->dofs_per_cell; ++k)
+    if (m->local_comp[k] == 0)
+      node[m->local_shape[k]] = dofs[k];
+}
+
+/* stress.cpp:141-200 — block-diagonal mass matrix; every diagonal block is the same scalar
+ * matrix, stored here once on the rows/columns [0,N) of the monolithic pattern. */
+static void stress_mass_matrix(const orc_mesh *m, double *values)
+{
+  const int ns = m->n_s, nq = m->n_q;
+  memset(values, 0, sizeof(double) * m->nnz);
+  for (int64_t cell = 0; cell < m->n_cells; ++cell)
+    {
+      const double *vtx = m->cell_vertices + cell * 8;
+      const double hx = vtx[2] - vtx[0], hy = vtx[5] - vtx[1];
+      int32_t node[MAXQ];
+      double local_matrix[MAXQ][MAXQ];
+      scalar_cell_nodes(m, cell, node);
+      memset(local_matrix, 0, sizeof(local_matrix));
+      for (int q = 0; q < nq; ++q)
+        {
+          const double JxW = m->qw[q] * hx * hy;
+          for (int i = 0; i < ns; ++i)
+            for (int j = 0; j < ns; ++j)
+              local_matrix[i][j] += m->shape[q * ns + i] * m->shape[q * ns + j] * JxW; /* :183-187 */
+        }
+      /* stress.cpp:193-196 [dealii-ext distribute_local_to_global, identity constraints] */
+      for (int i = 0; i < ns; ++i)
+        {
+          const int32_t gi = m->master[node[i]] >= 0 ? m->master[node[i]] : node[i];
+          for (int j = 0; j < ns; ++j)
+            {
+              const int32_t gj = m->master[node[j]] >= 0 ? m->master[node[j]] : node[j];
+              values[csr_find(m, gi, gj)] += local_matrix[i][j];
+            }
+          if (m->master[node[i]] >= 0)
+            values[csr_find(m, node[i], node[i])] += fabs(local_matrix[i][i]);
+        }
+    }
+}
+
+/* stress.cpp:204-314 — right-hand side of the L2 projection, rhs[c*N + t] */
+static void stress_rhs(const orc_mesh *m, const double *Psi, double eps, double *rhs)
+{
+  const int ns = m->n_s, nq = m->n_q, dpc = m->dofs_per_cell;
+  const int64_t N = m->N;
+  memset(rhs, 0, sizeof(double) * 4 * N);
+  for (int64_t cell = 0; cell < m->n_cells; ++cell)
+    {
+      const int32_t *dofs = m->cell_dofs + cell * dpc;
+      const double *vtx = m->cell_vertices + cell * 8;
+      const double hx = vtx[2] - vtx[0], hy = vtx[5] - vtx[1];
+      int32_t node[MAXQ];
+      double local_rhs[4][MAXQ];
+      scalar_cell_nodes(m, cell, node);
+      memset(local_rhs, 0, sizeof(local_rhs));
+      for (int q = 0; q < nq; ++q)
+        {
+          /* stress.cpp:262-267 */
+          double psi = 0, chi = 0, grad_psi[2] = {0, 0}, grad_chi[2] = {0, 0};
+          for (int k = 0; k < dpc; ++k)
+            {
+              const int c = m->local_comp[k], a = m->local_shape[k];
+              const double u = Psi[dofs[k]];
+              const double Nv = m->shape[q * ns + a];
+              const double gx = m->dshape[(q * ns + a) * 2 + 0] / hx, gy = m->dshape[(q * ns + a) * 2 + 1] / hy;
+              if (c == 0)
+                {
+                  psi += u * Nv;
+                  grad_psi[0] += u * gx;
+                  grad_psi[1] += u * gy;
+                }
+              else if (c == 1)
+                {
+                  chi += u * Nv;
+                  grad_chi[0] += u * gx;
+                  grad_chi[1] += u * gy;
+                }
+            }
+          const double JxW = m->qw[q] * hx * hy;
+          const double G[2] = {grad_psi[0] + grad_chi[0], grad_psi[1] + grad_chi[1]};
+          for (int a = 0; a < 2; ++a)
+            for (int b = 0; b < 2; ++b)
+              for (int i = 0; i < ns; ++i)
+                {
+                  /* the shape function of component (a,b) on scalar shape i:
+                   * tau = N e_a (x) e_b, (div tau)_a = d_b N [dealii-ext Tensor<2> view],
+                   * tr tau = delta_ab N, grad tr tau = delta_ab grad N (stress.cpp:271-280) */
+                  const double Nv = m->shape[q * ns + i];
+                  const double gN[2] = {m->dshape[(q * ns + i) * 2 + 0] / hx, m->dshape[(q * ns + i) * 2 + 1] / hy};
+                  const double tr = (a == b) ? Nv : 0.0;
+                  double v = Nv * (G[a] * grad_psi[b] + grad_psi[a] * G[b]);             /* :284-289 */
+                  v += gN[b] * (psi + chi) * grad_psi[a];                                   /* :291 */
+                  v += 0.5 * tr * (chi * chi + (1 + eps) * psi * psi + 0.5 * psi * psi * psi * psi); /* :293-295 */
+                  if (a == b)
+                    v -= (gN[0] * grad_psi[0] + gN[1] * grad_psi[1]) * psi;                 /* :297 */
+                  v -= tr * (grad_psi[0] * grad_psi[0] + grad_psi[1] * grad_psi[1]);       /* :299 */
+                  local_rhs[a * 2 + b][i] += v * JxW;
+                }
+        }
+      for (int c = 0; c < 4; ++c)
+        for (int i = 0; i < ns; ++i)
+          {
+            const int32_t gi = m->master[node[i]] >= 0 ? m->master[node[i]] : node[i];
+            rhs[c * N + gi] += local_rhs[c][i];
+          }
+    }
+}
+
+/* [dealii-ext] SolverCG with PreconditionIdentity as called at stress.cpp:319-333: x0 = 0,
+ * absolute tolerance tol on ||b - A x||, at most max_iters steps. */
+static int64_t stress_cg(const orc_mesh *m, const double *values, const double *b, double *x, double tol,
+                         int64_t max_iters, int *converged)
+{
+  const int64_t N = m->N;
+  double *g = (double *)xmalloc(sizeof(double) * N), *d = (double *)xmalloc(sizeof(double) * N);
+  double *h = (double *)xmalloc(sizeof(double) * N);
+  memset(x, 0, sizeof(double) * N);
+  for (int64_t i = 0; i < N; ++i)
+    g[i] = -b[i];
+  double res = sqrt(vdot(N, g, g));
+  int64_t it = 0;
+  int state = control_check(0, res, tol, max_iters);
+  if (state == 0)
+    {
+      for (int64_t i = 0; i < N; ++i)
+        d[i] = -g[i];
+      double gh = res * res;
+      while (state == 0)
+        {
+          it++;
+          for (int64_t r = 0; r < N; ++r)
+            {
+              double s = 0;
+              for (int64_t k = m->row_ptr[r]; k < m->row_ptr[r + 1] && m->col_idx[k] < N; ++k)
+                s += values[k] * d[m->col_idx[k]];
+              h[r] = s;
+            }
+          const double alpha = gh / vdot(N, d, h);
+          vaxpy(N, x, alpha, d);
+          vaxpy(N, g, alpha, h);
+          res = sqrt(vdot(N, g, g));
+          state = control_check(it, res, tol, max_iters);
+          if (state != 0)
+            break;
+          const double beta = res * res / gh;
+          gh = res * res;
+          for (int64_t i = 0; i < N; ++i)
+            d[i] = beta * d[i] - g[i];
+        }
+    }
+  *converged = (state == 1);
+  free(g);
+  free(d);
+  free(h);
+  return it;
+}
+
+int orc_stress(const orc_mesh *m, const double *Psi, double eps, double tol, double *stress,
+               int64_t *cg_iters, double *rhs_out)
+{
+  const int64_t N = m->N;
+  double *values = (double *)xmalloc(sizeof(double) * m->nnz);
+  double *rhs = (double *)xmalloc(sizeof(double) * 4 * N);
+  int ok = 1;
+  stress_mass_matrix(m, values);
+  stress_rhs(m, Psi, eps, rhs);
+  if (rhs_out)
+    memcpy(rhs_out, rhs, sizeof(double) * 4 * N);
+  for (int c = 0; c < 4; ++c) /* stress.cpp:327-334; SolverControl(n_dofs) of the 4N-dof handler */
+    {
+      int conv = 0;
+      cg_iters[c] = stress_cg(m, values, rhs + c * N, stress + c * N, tol, 4 * N, &conv);
+      ok &= conv;
+    }
+  /* stress.cpp:336 — constraints.distribute */
+  for (int c = 0; c < 4; ++c)
+    for (int64_t t = 0; t < N; ++t)
+      if (m->master[t] >= 0)
+        stress[c * N + t] = stress[c * N + m->master[t]];
+  free(values);
+  free(rhs);
+  return ok ? 0 : 2;
+}

@@ -13,6 +13,7 @@
  *   mpi.cpp = src/phase_field_crystal_systems/phase_field_crystal_system_mpi.cpp
  *   hex.cpp = src/phase_field_functions/hexagonal_lattice.cpp
  *   app.cpp = app/simulations/phase_field_crystal_simulation_mpi.cpp
+ *   stress.cpp = src/stress_tools/stress_calculator_mpi.cpp
  * [dealii-ext] marks behaviour of deal.II (>= 9.3, not vendored in the reference) that is
  * restated from its published algorithms.
  */
@@ -88,6 +89,14 @@ int orc_newton_step(const orc_mesh *m, double *Psi_n, double *Psi_n1, double dt,
 
 /* mpi.cpp:485 — slave dof := master dof */
 void orc_distribute(const orc_mesh *m, double *v);
+
+/* stress.cpp:141-200 (mass matrix), 204-314 (right-hand side), 317-341 (one unpreconditioned CG
+ * per tensor component, then constraints.distribute).  stress[c*N + t]: component c = a*2 + b of
+ * the L2-projected stress on scalar node t.  cg_iters[4] = SolverControl::last_step() per
+ * component; rhs_out (optional, [4N]) receives the assembled right-hand side.
+ * Returns 0, or 2 if a CG solve would throw NoConvergence. */
+int orc_stress(const orc_mesh *m, const double *Psi, double eps, double tol, double *stress,
+               int64_t *cg_iters, double *rhs_out);
 
 int orc_max_threads(void);
 void orc_set_threads(int n);
