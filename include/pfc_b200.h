@@ -191,6 +191,21 @@ int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms3, double *bytes2);
 /* consistency of redundant kernel forms on a deterministic pseudo-random field (lattice path: K product as node
  * stencil vs cell quadrature); max_rel = max |a - b| / max |a|.  0 when the handle has no redundant form. [collective] */
 int pfc_selfcheck(pfc_handle *h, double *max_rel);
+
+/* ---- stress projection ------------------------------------------------------
+ * Replaces StressCalculatorMPI<dim>::calculate_stress(mpi_communicator, Psi_dof_handler, Psi, eps)
+ * (src/stress_tools/stress_calculator_mpi.cpp:345-353 = calculate_righthand_side :204-314 + solve
+ * :317-341, with the mass matrix of calculate_mass_matrix :141-200) for Psi = the handle's current
+ * Psi_n, which is read where the time stepper left it in HBM.
+ *   stress   [4][N], N = n_dofs / 3: component c = a*2 + b of the L2-projected stress at scalar node t
+ *            (the node carrying psi dof block_start[0] + t) at stress[c*N + t]; like pfc_get_state,
+ *            a rank fills the nodes it owns and leaves the others 0.  Periodic images carry the value of their master (:336).
+ *   cg_iters [4]: SolverControl::last_step() of each component's SolverCG (:329-334).
+ *   tol:     absolute tolerance on ||b - M x||_2 (SolverControl default 1e-10, :320); at most 4 N steps.
+ * Needs the lattice path (operator_kind = PFC_OPERATOR_MATRIX_FREE on a uniform periodic mesh);
+ * PFC_ERR_UNSUPPORTED otherwise, PFC_ERR_GMRES_NOT_CONVERGED where the reference's SolverCG would throw
+ * NoConvergence.  [collective] */
+int pfc_stress(pfc_handle *h, double eps, double tol, double *stress, int64_t *cg_iters);
 /* the two Gram-Schmidt kernels at Krylov dimension dim (1..restart): multi-dot (reads dim+1
  * vectors) and multi-axpy with norm (reads dim+1, writes 1) */
 int pfc_time_krylov(pfc_handle *h, int32_t dim, int32_t reps, double *ms_dot, double *bytes_dot,

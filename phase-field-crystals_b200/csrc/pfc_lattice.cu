@@ -107,6 +107,18 @@ int lat_launch(pfc_handle *h, int mode, const LatOp &op, const Ctl *ctl)
     case LAT_S: return q1 ? launch_mode<1, LAT_S>(h, op, ctl) : launch_mode<2, LAT_S>(h, op, ctl);
     case LAT_K: return q1 ? launch_mode<1, LAT_K>(h, op, ctl) : launch_mode<2, LAT_K>(h, op, ctl);
     case LAT_R: return q1 ? launch_mode<1, LAT_R>(h, op, ctl) : launch_mode<2, LAT_R>(h, op, ctl);
+    case LAT_T: return q1 ? launch_mode<1, LAT_T>(h, op, ctl) : launch_tile<2, LAT_T, 16, 8>(h, op, ctl);
+    case LAT_M:
+      {
+        const LatGeom &G = h->lat_geom;
+        const dim3 grid((G.w + 127) / 128, (G.h + 3) / 4, 4);
+        if (q1)
+          lat_mass_kernel<1, 128, 4><<<grid, 128, 0, h->stream>>>(G, op);
+        else
+          lat_mass_kernel<2, 128, 4><<<grid, 128, 0, h->stream>>>(G, op);
+        h->launches++;
+        return PFC_OK;
+      }
     }
   return h->fail(PFC_ERR_BAD_ARGUMENT, "lat_launch: unknown mode");
 }
@@ -120,6 +132,8 @@ double lat_bytes(const pfc_handle *h, int mode)
     case LAT_J: return 64.0 * N;  // x 24 + y 24 + psi, chi 16
     case LAT_S: return 80.0 * N;  // v0, v1, v2, psi, chi 40 + add, dinv, d 24 + d, out 16   (Chebyshev step)
     case LAT_K: return 32.0 * N;  // v 8 + add 8 + inv_ml 8 + out 8
+    case LAT_T: return 48.0 * N;  // psi, chi 16 + four right-hand sides 32
+    case LAT_M: return 64.0 * N;  // four fields in, four out
     default: return (h->prm.theta == 1.0 ? 32.0 : 48.0) * N + 32.0 * N; // state in, rhs + 1/diag(B) out
     }
 }

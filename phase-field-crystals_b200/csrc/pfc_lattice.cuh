@@ -174,8 +174,8 @@ __device__ __forceinline__ int32_t lat_id(const LatGeom &L, int ex, int ey)
 template <int MODE>
 struct LatShape
 {
-  static constexpr int NF = MODE == LAT_J ? 5 : (MODE == LAT_S ? 5 : (MODE == LAT_K ? 1 : 6));
-  static constexpr int NOUT = MODE == LAT_J ? 3 : (MODE == LAT_R ? 4 : 1);
+  static constexpr int NF = MODE == LAT_J ? 5 : (MODE == LAT_S ? 5 : (MODE == LAT_K ? 1 : (MODE == LAT_T ? 2 : 6)));
+  static constexpr int NOUT = MODE == LAT_J ? 3 : ((MODE == LAT_R || MODE == LAT_T) ? 4 : 1);
 };
 
 template <int P, int MODE, int CX, int CY>
@@ -240,6 +240,11 @@ static __global__ void __launch_bounds__(CX *CY) lat_kernel(LatGeom L, LatOp O, 
               }
             else if constexpr (MODE == LAT_K)
               f[it][0] = O.s0[u];
+            else if constexpr (MODE == LAT_T)
+              {
+                f[it][0] = O.in3a[vaddr(u, 0, Np)];
+                f[it][1] = O.in3a[vaddr(u, 1, Np)];
+              }
             else
               {
 #pragma unroll
@@ -412,6 +417,62 @@ static __global__ void __launch_bounds__(CX *CY) lat_kernel(LatGeom L, LatOp O, 
           lat_test<P, true, true>(A0, gx, gy, ihx, ihy, y0);
           store_y(0, y0);
         }
+    }
+  else if constexpr (MODE == LAT_T)
+    { // right-hand side of the stress projection (stress_calculator_mpi.cpp:283-300).  The shape function of tensor
+      // component (a,b) on scalar shape N is tau = N e_a (x) e_b: tau : X = N X_ab, (div tau)_a = d_b N,
+      // tr tau = delta_ab N, grad tr tau = delta_ab grad N.  With P = grad psi, G = grad (psi + chi), S = psi + chi:
+      //   rhs_ab = int N (G_a P_b + P_a G_b) + d_b N S P_a + delta_ab [ N (F - |P|^2) - psi grad N . P ]
+      //   F = (chi^2 + (1 + eps) psi^2 + psi^4 / 2) / 2
+      double psi[n][n], px[n][n], py[n][n], A[n][n], cx_[n][n], cy_[n][n];
+      load_u(0, u);
+      lat_interp<P, true, true>(u, ihx, ihy, psi, px, py);
+      load_u(1, u);
+      lat_interp<P, true, true>(u, ihx, ihy, v, gx, gy); // chi, then G = grad psi + grad chi
+      double D[n][n], S[n][n];                            // D = F - |P|^2
+#pragma unroll
+      for (int a = 0; a < n; ++a)
+#pragma unroll
+        for (int b = 0; b < n; ++b)
+          {
+            const double p_ = psi[a][b], c_ = v[a][b], p2 = p_ * p_;
+            gx[a][b] += px[a][b];
+            gy[a][b] += py[a][b];
+            S[a][b] = p_ + c_;
+            D[a][b] = 0.5 * (c_ * c_ + (1.0 + O.eps) * p2 + 0.5 * p2 * p2) - (px[a][b] * px[a][b] + py[a][b] * py[a][b]);
+          }
+      sfor<4>([&](auto C) {
+        PFC_IC(c, C);
+        constexpr int ta = c / 2, tb = c % 2;
+        double y[n][n] = {};
+#pragma unroll
+        for (int a = 0; a < n; ++a)
+#pragma unroll
+          for (int b = 0; b < n; ++b)
+            {
+              const double Pa = ta == 0 ? px[a][b] : py[a][b], Pb = tb == 0 ? px[a][b] : py[a][b];
+              const double Ga = ta == 0 ? gx[a][b] : gy[a][b], Gb = tb == 0 ? gx[a][b] : gy[a][b];
+              double av = Ga * Pb + Pa * Gb, dx = 0.0, dy = 0.0;
+              if (tb == 0)
+                dx = S[a][b] * Pa;
+              else
+                dy = S[a][b] * Pa;
+              if (ta == tb)
+                {
+                  av += D[a][b];
+                  dx -= psi[a][b] * px[a][b];
+                  dy -= psi[a][b] * py[a][b];
+                }
+              A[a][b] = av;
+              cx_[a][b] = dx;
+              cy_[a][b] = dy;
+            }
+        jxw(A, 1.0);
+        jxw(cx_, 1.0);
+        jxw(cy_, 1.0);
+        lat_test<P, true, true>(A, cx_, cy_, ihx, ihy, y);
+        store_y(c, y);
+      });
     }
   else
     { // LAT_R: -R and diag(B); fields 0..2 = (psi, chi, phi)_n, 3..5 = (psi, chi, phi)_{n-1}
@@ -623,6 +684,12 @@ static __global__ void __launch_bounds__(CX *CY) lat_kernel(LatGeom L, LatOp O, 
           else
             O.out[r] = e_dinv[it] * val[0];
         }
+      else if constexpr (MODE == LAT_T)
+        {
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+            O.out[c * O.zstride + r] = val[c];
+        }
       else
         {
           O.out3[r] = val[0];
@@ -744,6 +811,67 @@ static __global__ void __launch_bounds__(kKsX) lat_kstencil_kernel(LatGeom L, La
       O.out[r] = res;
       if (O.out2)
         O.out2[r] = res;
+    }
+}
+
+// out_c = M v_c for the batched scalar fields c of zmask (blockIdx.z): consistent mass matrix Mx (x) My, same
+// thread layout as the K stencil above.
+template <int P, int kKsX, int kKsY>
+static __global__ void __launch_bounds__(kKsX) lat_mass_kernel(LatGeom L, LatOp O)
+{
+  if (!((O.zmask >> blockIdx.z) & 1))
+    return;
+  constexpr int R = kKsY + 2 * P;
+  const int lx = blockIdx.x * kKsX + threadIdx.x, ly0 = blockIdx.y * kKsY;
+  if (lx >= L.w)
+    return;
+  const double *__restrict__ v = O.s0 + blockIdx.z * O.zstride;
+  double *__restrict__ out = O.out + blockIdx.z * O.zstride;
+  const int midx = (P == 2) ? ((L.ex0 + lx) & 1) : 0;
+  double mx[2 * P + 1];
+  sfor<2 * P + 1>([&](auto DD) {
+    PFC_IC(dd, DD);
+    mx[dd] = (midx ? Row1<P>::M(1, dd - P) : Row1<P>::M(0, dd - P)) * L.hx;
+  });
+  double rM[R];
+  const bool interior = lx - P >= 0 && lx + P < L.w && ly0 - P >= 0 && ly0 + kKsY - 1 + P < L.h;
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+    {
+      double sm = 0;
+      if (interior)
+        {
+          const double *p0 = v + (int64_t)(ly0 - P + r) * L.w + lx;
+#pragma unroll
+          for (int dd = 0; dd <= 2 * P; ++dd)
+            sm = fma(mx[dd], __ldg(p0 + (dd - P)), sm);
+        }
+      else
+        {
+          const int ey = min(max(L.ey0 + ly0 - P + r, 0), L.fh - 1);
+#pragma unroll
+          for (int dd = 0; dd <= 2 * P; ++dd)
+            {
+              const int ex = min(max(L.ex0 + lx + dd - P, 0), L.fw - 1);
+              sm = fma(mx[dd], v[lat_id(L, ex, ey)], sm);
+            }
+        }
+      rM[r] = sm;
+    }
+#pragma unroll
+  for (int j = 0; j < kKsY; ++j)
+    {
+      const int ly = ly0 + j;
+      if (ly >= L.h)
+        break;
+      const int midy = (P == 2) ? ((L.ey0 + ly) & 1) : 0;
+      double s = 0;
+      sfor<2 * P + 1>([&](auto DD) {
+        PFC_IC(dd, DD);
+        const double my = (midy ? Row1<P>::M(1, dd - P) : Row1<P>::M(0, dd - P)) * L.hy;
+        s = fma(my, rM[j + dd], s);
+      });
+      out[(int64_t)ly * L.w + lx] = s;
     }
 }
 

@@ -22,7 +22,11 @@ enum
   LAT_J = 0, // y = J x                       (vec3 in3a = x, state in3b; out3 = y)
   LAT_S = 1, // y0 = sB B v0 + sC C v1 + sD D v2 on scalar fields, epilogue `epi` (see bcd_kernel, pfc_precond.cuh)
   LAT_K = 2, // out = (a add + k K s0) inv_ml  (kmv_kernel)
-  LAT_R = 3  // out3 = -R(Psi_n = in3a, Psi_n-1 = in3b), out = 1 / diag(B)   (assemble_system, mpi.cpp:388-417)
+  LAT_R = 3, // out3 = -R(Psi_n = in3a, Psi_n-1 = in3b), out = 1 / diag(B)   (assemble_system, mpi.cpp:388-417)
+  LAT_T = 4, // out[c zstride + r] = right-hand side of the stress projection, c = a*2 + b, from the state in3a
+             // (stress_calculator_mpi.cpp:204-314)
+  LAT_M = 5  // out[c zstride + r] = (M s0[c zstride + .])_r for the fields of zmask: consistent mass matrix as a
+             // node stencil (stress_calculator_mpi.cpp:141-200)
 };
 
 struct LatOp
@@ -34,6 +38,8 @@ struct LatOp
   double a, k, sB, sC, sD;
   double dt, theta, eps;
   int epi;
+  int64_t zstride; // LAT_T / LAT_M: doubles between the batched scalar fields (tensor components)
+  int zmask;       // LAT_M: bit c set = field c is processed
 };
 
 

@@ -1,0 +1,255 @@
+// pfc_stress.cu — L2 projection of the PFC stress tensor on the lattice path.
+// Replaces StressCalculatorMPI<dim>::calculate_stress (src/stress_tools/stress_calculator_mpi.cpp:345-353):
+//   calculate_mass_matrix  :141-200   -> consistent mass matrix as a node stencil (LAT_M), never stored
+//   calculate_righthand_side :204-314 -> one thread-per-cell kernel for all dim*dim components (LAT_T)
+//   solve                  :317-341   -> the dim*dim unpreconditioned CG solves run as ONE batched iteration
+//                                        (independent alpha/beta per component, converged components masked
+//                                        out, so every component sees exactly its own CG iterates), then
+//                                        constraints.distribute
+// The state is read where the time stepper left it in HBM; only the 4 N results travel to the host.
+#include <algorithm>
+#include <cmath>
+#include <vector>
+
+#include "pfc_comm.h"
+#include "pfc_handle.h"
+#include "pfc_krylov.cuh"
+#include "pfc_lattice_args.h"
+
+using namespace pfc;
+
+#define PFC_TRY(expr)    \
+  do                     \
+    {                    \
+      int rc_ = (expr);  \
+      if (rc_ != PFC_OK) \
+        return rc_;      \
+    }                    \
+  while (0)
+
+namespace
+{
+struct Four
+{
+  double v[4];
+};
+
+// g = -b, d = b (b arrives in d), out[c] = b_c . b_c
+__global__ void __launch_bounds__(kVecThreads) stress_init_kernel(double *__restrict__ g, const double *__restrict__ d,
+                                                                  int64_t zstride, int64_t n, double *partial,
+                                                                  double *out, unsigned int *counter)
+{
+  double acc[4] = {0, 0, 0, 0};
+  for (int64_t i = (int64_t)blockIdx.x * kVecThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kVecThreads)
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      {
+        const double b = d[c * zstride + i];
+        g[c * zstride + i] = -b;
+        acc[c] = fma(b, b, acc[c]);
+      }
+  grid_reduce<4>(acc, partial, out, counter, ArDev{});
+}
+
+// out[c] = d_c . h_c for the components of mask
+__global__ void __launch_bounds__(kVecThreads) stress_dot_kernel(const double *__restrict__ d, const double *__restrict__ hh,
+                                                                 int64_t zstride, int64_t n, int mask, double *partial,
+                                                                 double *out, unsigned int *counter)
+{
+  double acc[4] = {0, 0, 0, 0};
+  for (int64_t i = (int64_t)blockIdx.x * kVecThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kVecThreads)
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if ((mask >> c) & 1)
+        acc[c] = fma(d[c * zstride + i], hh[c * zstride + i], acc[c]);
+  grid_reduce<4>(acc, partial, out, counter, ArDev{});
+}
+
+// alpha_c = gh_c / dh_c;  x_c += alpha_c d_c;  g_c += alpha_c h_c;  out[c] = g_c . g_c
+__global__ void __launch_bounds__(kVecThreads) stress_update_kernel(double *__restrict__ x, double *__restrict__ g,
+                                                                    const double *__restrict__ d,
+                                                                    const double *__restrict__ hh, int64_t zstride,
+                                                                    int64_t n, int mask, Four gh, const double *dh,
+                                                                    double *partial, double *out, unsigned int *counter)
+{
+  double acc[4] = {0, 0, 0, 0}, alpha[4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+    alpha[c] = ((mask >> c) & 1) ? gh.v[c] / dh[c] : 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * kVecThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kVecThreads)
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if ((mask >> c) & 1)
+        {
+          const int64_t k = c * zstride + i;
+          x[k] = fma(alpha[c], d[k], x[k]);
+          const double gv = fma(alpha[c], hh[k], g[k]);
+          g[k] = gv;
+          acc[c] = fma(gv, gv, acc[c]);
+        }
+  grid_reduce<4>(acc, partial, out, counter, ArDev{});
+}
+
+// d_c = beta_c d_c - g_c
+__global__ void __launch_bounds__(kVecThreads) stress_dir_kernel(double *__restrict__ d, const double *__restrict__ g,
+                                                                 int64_t zstride, int64_t n, int mask, Four beta)
+{
+  for (int64_t i = (int64_t)blockIdx.x * kVecThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kVecThreads)
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if ((mask >> c) & 1)
+        {
+          const int64_t k = c * zstride + i;
+          d[k] = fma(beta.v[c], d[k], -g[k]);
+        }
+}
+
+// constraints.distribute (stress_calculator_mpi.cpp:336): v_c[slave] = v_c[master]
+__global__ void stress_distribute_kernel(double *v, const int32_t *slave, const int32_t *master, int64_t n, int64_t zstride)
+{
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n)
+    return;
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+    v[c * zstride + slave[k]] = v[c * zstride + master[k]];
+}
+
+int read4(pfc_handle *h, double *dev, double *host4)
+{
+  PFC_TRY(allreduce_sum(h, dev, 4));
+  PFC_CUDA(h, cudaMemcpyAsync(h->h_scalar, dev, 4 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+  for (int c = 0; c < 4; ++c)
+    host4[c] = h->h_scalar[c];
+  return PFC_OK;
+}
+} // namespace
+
+extern "C" int pfc_stress(pfc_handle *h, double eps, double tol, double *stress, int64_t *cg_iters)
+{
+  if (!h || !stress || !cg_iters)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->is_setup || !h->has_state)
+    return h->fail(PFC_ERR_STATE, "pfc_stress needs pfc_setup and pfc_set_state first");
+  if (!h->lat)
+    return h->fail(PFC_ERR_UNSUPPORTED,
+                   "pfc_stress runs on the lattice path (operator_kind = PFC_OPERATOR_MATRIX_FREE on a uniform periodic mesh)");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  const Plan &P = h->plan;
+  cudaStream_t s = h->stream;
+  const int64_t ss = (P.Np + P.n_ghost + 15) / 16 * 16, Np = P.Np;
+  const int64_t N = P.n_dofs / 3;
+  if (h->d_stress.n != (size_t)(16 * ss + 16))
+    {
+      PFC_CUDA(h, h->d_stress.alloc((size_t)(16 * ss + 16)));
+      // API node t -> address in a batched scalar field, owned nodes only (like pfc_get_state)
+      std::vector<int64_t> map((size_t)4 * N, -1);
+      for (int64_t r = 0; r < Np; ++r)
+        if (P.perm[r] >= 0)
+          for (int c = 0; c < 4; ++c)
+            map[c * N + P.perm[r]] = c * ss + r;
+      PFC_CUDA(h, h->d_stress_map.upload(map, s));
+      PFC_CUDA(h, h->d_stress_io.alloc((size_t)4 * N));
+      PFC_CUDA(h, cudaStreamSynchronize(s));
+    }
+  double *x = h->d_stress.p, *g = x + 4 * ss, *d = x + 8 * ss, *hh = x + 12 * ss, *small = x + 16 * ss;
+  double *dh = small, *rr = small + 4;
+  PFC_CUDA(h, cudaMemsetAsync(x, 0, (size_t)(16 * ss + 16) * sizeof(double), s));
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((Np + kVecThreads - 1) / kVecThreads, 4 * (int64_t)h->n_sm));
+
+  // right-hand side (all four components in one pass over the state), into d
+  PFC_TRY(halo_exchange(h, h->d_psi_n.p));
+  {
+    LatOp o = lat_op(h);
+    o.eps = eps;
+    o.in3a = h->d_psi_n.p;
+    o.out = d;
+    o.zstride = ss;
+    PFC_TRY(lat_launch(h, LAT_T, o, nullptr));
+  }
+  stress_init_kernel<<<grid, kVecThreads, 0, s>>>(g, d, ss, Np, h->d_partial.p, rr, h->d_counter.p);
+  h->launches++;
+  double r4[4], gh[4];
+  PFC_TRY(read4(h, rr, r4));
+  // SolverControl(dof_handler.n_dofs()) of the dim*dim-component handler, default tolerance (stress.cpp:320)
+  const int64_t max_iters = 4 * (P.n_dofs / 3);
+  int mask = 0;
+  for (int c = 0; c < 4; ++c)
+    {
+      cg_iters[c] = 0;
+      gh[c] = r4[c];
+      if (!std::isfinite(r4[c]))
+        return h->fail(PFC_ERR_NONFINITE, "pfc_stress: non-finite right-hand side");
+      if (std::sqrt(r4[c]) > tol)
+        mask |= 1 << c;
+    }
+  int64_t it = 0;
+  while (mask)
+    {
+      ++it;
+      if (P.n_ranks > 1)
+        for (int c = 0; c < 4; ++c)
+          if ((mask >> c) & 1)
+            PFC_TRY(halo_exchange_scalar(h, d + c * ss));
+      {
+        LatOp o = lat_op(h);
+        o.s0 = d;
+        o.out = hh;
+        o.zstride = ss;
+        o.zmask = mask;
+        PFC_TRY(lat_launch(h, LAT_M, o, nullptr));
+      }
+      stress_dot_kernel<<<grid, kVecThreads, 0, s>>>(d, hh, ss, Np, mask, h->d_partial.p, dh, h->d_counter.p);
+      PFC_TRY(allreduce_sum(h, dh, 4));
+      Four ghv, beta;
+      for (int c = 0; c < 4; ++c)
+        ghv.v[c] = gh[c];
+      stress_update_kernel<<<grid, kVecThreads, 0, s>>>(x, g, d, hh, ss, Np, mask, ghv, dh, h->d_partial.p, rr,
+                                                       h->d_counter.p);
+      h->launches += 2;
+      PFC_TRY(read4(h, rr, r4));
+      for (int c = 0; c < 4; ++c)
+        {
+          beta.v[c] = 0.0;
+          if (!((mask >> c) & 1))
+            continue;
+          const double res = std::sqrt(r4[c]);
+          if (res <= tol)
+            {
+              cg_iters[c] = it;
+              mask &= ~(1 << c);
+            }
+          else if (it >= max_iters || !std::isfinite(res))
+            return h->fail(PFC_ERR_GMRES_NOT_CONVERGED, "pfc_stress: CG did not converge in %lld iterations (component %d, residual %.3e)",
+                           (long long)it, c, res);
+          else
+            {
+              beta.v[c] = r4[c] / gh[c];
+              gh[c] = r4[c];
+            }
+        }
+      if (mask)
+        {
+          stress_dir_kernel<<<grid, kVecThreads, 0, s>>>(d, g, ss, Np, mask, beta);
+          h->launches++;
+        }
+    }
+  // constraints.distribute, then the API order
+  if (P.n_ranks > 1)
+    for (int c = 0; c < 4; ++c)
+      PFC_TRY(halo_exchange_scalar(h, x + c * ss));
+  const int64_t nsl = (int64_t)P.slave_id.size();
+  if (nsl > 0)
+    {
+      stress_distribute_kernel<<<(int)((nsl + 255) / 256), 256, 0, s>>>(x, h->d_slave.p, h->d_slave_master.p, nsl, ss);
+      h->launches++;
+    }
+  PFC_CUDA(h, cudaMemsetAsync(h->d_stress_io.p, 0, (size_t)4 * N * sizeof(double), s));
+  gather_kernel<<<(int)((4 * N + 255) / 256), 256, 0, s>>>(h->d_stress_io.p, x, h->d_stress_map.p, 4 * N, 4 * ss);
+  h->launches++;
+  PFC_CUDA(h, cudaGetLastError());
+  PFC_CUDA(h, cudaMemcpyAsync(stress, h->d_stress_io.p, (size_t)4 * N * sizeof(double), cudaMemcpyDeviceToHost, s));
+  PFC_CUDA(h, cudaStreamSynchronize(s));
+  return PFC_OK;
+}

@@ -24,6 +24,7 @@ A = P.LATTICE_A
 def main():
     degree, n_refines, steps = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
     kw = json.loads(sys.argv[4]) if len(sys.argv) > 4 else {}
+    check_stress = kw.pop("check_stress", 0)
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -58,6 +59,16 @@ def main():
             print(f"[{world} ranks] Q{degree} 2^{n_refines} step {step}: gmres gpu {st['gmres_iters']} oracle {ref['gmres_iters']} "
                   f"rel L2 psi {err:.2e} all {err_all:.2e}", flush=True)
             ok = ok and st["status"] == 0 and err <= 1e-9 and err_all <= 1e-9
+    if check_stress:  # stress projection of the stepped state, owned nodes summed over the ranks
+        sg, its = s.stress(-0.8)
+        mine = torch.from_numpy(sg).cuda()
+        dist.all_reduce(mine)
+        sg = mine.cpu().numpy()
+        if rank == 0:
+            o = om.stress(Pn, -0.8)
+            err = np.abs(sg - o["stress"]).max() / np.abs(o["stress"]).max()
+            print(f"[{world} ranks] stress: CG its gpu {its} oracle {o['cg_iters']} max rel diff {err:.2e}", flush=True)
+            ok = ok and o["status"] == 0 and err <= 1e-8 and all(abs(a - b) <= 1 for a, b in zip(its, o["cg_iters"]))
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, src=0)
     s.close()

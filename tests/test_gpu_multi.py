@@ -17,7 +17,8 @@ def _n_gpus():
 @pytest.mark.parametrize("degree,n_refines,steps,extra", [(1, 5, 2, "{}"), (2, 4, 1, "{}"), (1, 4, 1, '{"use_cuda_graph": 0}'),
                                                           (1, 5, 2, '{"preconditioner": 1}'), (2, 4, 1, '{"preconditioner": 1}'),
                                                           (1, 5, 2, '{"operator_kind": 1}'), (2, 4, 2, '{"operator_kind": 1, "preconditioner": 1}'),
-                                                          (1, 5, 2, '{"operator_kind": 1, "preconditioner": 1}')])
+                                                          (1, 5, 2, '{"operator_kind": 1, "preconditioner": 1}'),
+                                                          (2, 4, 1, '{"operator_kind": 1, "preconditioner": 1, "check_stress": 1}')])
 @pytest.mark.parametrize("no_p2p", [0, 1])
 def test_ranks_match_oracle(built, degree, n_refines, steps, extra, no_p2p):
     """no_p2p = 0: halo exchange and all-reduce by the peer-memory kernels over NVLink; 1: NCCL."""

@@ -292,3 +292,36 @@ def test_hundred_steps_within_1e7(built, degree, n_refines, kw):
     print(f"100 steps Q{degree} 2^{n_refines} {kw}: rel L2 psi {_rel(got[:om.N], Pn[:om.N]):.2e} (worst at a multiple of 10: {worst:.2e})")
     assert _rel(got[:om.N], Pn[:om.N]) <= 1e-7 and _rel(got, Pn) <= 1e-7
     s.close()
+
+
+# ---- stress projection (stress_calculator_mpi.cpp:345-353) -------------------------------------
+@pytest.mark.parametrize("degree,n_refines", [(1, 5), (2, 4), (2, 5)])
+def test_stress_matches_oracle(built, degree, n_refines):
+    """Right-hand side kernel + mass stencil + batched CG against the oracle's assembled-matrix restatement:
+    same CG iteration counts per component, nodal stress to 1e-9 of its max (CG to 1e-10 absolute on both sides)."""
+    om, st, s, Psi = _setup(built, degree, n_refines, operator_kind=1, preconditioner=1)
+    s.set_state(Psi, Psi)
+    for _ in range(2):  # a state with chi, phi away from the initial condition
+        s.step()
+    state = s.get_state()
+    o = om.stress(state, EPS)
+    assert o["status"] == 0
+    got, its = s.stress(EPS)
+    print(f"stress Q{degree} 2^{n_refines}: CG its gpu {its} oracle {o['cg_iters']}, "
+          f"max |diff| {np.abs(got - o['stress']).max():.2e} of {np.abs(o['stress']).max():.2e}")
+    assert np.abs(got - o["stress"]).max() <= 1e-9 * np.abs(o["stress"]).max()
+    assert all(abs(a - b) <= 1 for a, b in zip(its, o["cg_iters"]))
+    # off-diagonal components differ (div tau term), periodic images equal their masters
+    assert np.abs(got[1] - got[2]).max() > 1e-3
+    sl = np.nonzero(om.master[:om.N] >= 0)[0]
+    assert np.array_equal(got[:, sl], got[:, om.master[sl]])
+    s.close()
+
+
+def test_stress_needs_the_lattice_path(built):
+    om, st, s, Psi = _setup(built, 1, 4)
+    s.set_state(Psi, Psi)
+    with pytest.raises(built.PfcError) as e:
+        s.stress(EPS)
+    assert e.value.code == 7 and "lattice" in str(e.value)
+    s.close()
