@@ -271,6 +271,13 @@ def main():
     kry = solver.time_krylov(dim=14, reps=10)
     ms_asm, bytes_asm = solver.time_assembly(reps=3)
     comm_legs = solver.time_comm(reps=50) if world > 1 else None
+    stress_leg = None
+    if args.mf:  # SURVEY.md 8f-1 (outside the timed region): stress projection of the final state, result to the host
+        solver.stress(EPS)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        _, cg_its = solver.stress(EPS)
+        stress_leg = {"ms_wall_incl_d2h": (time.perf_counter() - t0) * 1e3, "cg_iters": [int(i) for i in cg_its]}
     peak, peak_src = measured_peak()
     N = mesh.N
     nnz_csr = None
@@ -311,6 +318,8 @@ def main():
         }
         if comm_legs is not None:
             line["comm_legs_us"] = comm_legs
+        if stress_leg is not None:
+            line["stress_projection"] = stress_leg
         # the reference's monolithic CSR would move 12 nnz + 12 n_rows + 8 n_cols bytes for the same product
         if not args.mf:
             nnz_mono = 7 * (bytes_op - 48.0 * N) / 36.0  # approx: 7 blocks per stored scalar entry
