@@ -206,6 +206,29 @@ int pfc_selfcheck(pfc_handle *h, double *max_rel);
  * PFC_ERR_UNSUPPORTED otherwise, PFC_ERR_GMRES_NOT_CONVERGED where the reference's SolverCG would throw
  * NoConvergence.  [collective] */
 int pfc_stress(pfc_handle *h, double eps, double tol, double *stress, int64_t *cg_iters);
+
+/* ---- output -----------------------------------------------------------------
+ * Host-side writer replacing DataOut::build_patches() + write_vtu_with_pvtu_record(directory, basename,
+ * counter, comm, n_digits_for_counter = 2) as called by output_configuration / output_rhs (mpi.cpp:597-645)
+ * and StressCalculatorMPI::output_stress (stress_calculator_mpi.cpp:358-384): this rank's owned cells as
+ * VTK_QUADs with their 4 vertex values into <directory><basename>_<counter %02u>.<rank>.vtu, and on rank 0 the
+ * record <directory><basename>_<counter %02u>.pvtu naming all ranks' pieces.  directory and basename are
+ * concatenated as given (like the reference; pass "out/" to write into a folder).
+ *   values [n_fields][N] nodal fields by scalar node t (psi dof block_start[0] + t); the vertices of the owned
+ *          cells must be filled (owned + ghost nodes).
+ *   interpretation[f]: 0 component_is_scalar, 1 component_is_part_of_tensor (consecutive fields of one name
+ *          form one 9-component tensor array, 2-D component a*2 + b in slot a*3 + b); NULL = all scalar.
+ * No GPU involved.  Returns PFC_OK or PFC_ERR_BAD_ARGUMENT with a message in err. */
+int pfc_vtu_write(const pfc_mesh *mesh, const char *directory, const char *basename, uint32_t counter,
+                  int32_t n_fields, const char *const *names, const int32_t *interpretation,
+                  const double *values, char *err, int32_t errlen);
+/* file name of the piece of `rank` (rank < 0: of the .pvtu record), without directory */
+int pfc_vtu_piece_name(const char *basename, uint32_t counter, int32_t rank, int32_t n_ranks, char *out, int32_t outlen);
+/* download (owned + ghost values) and write: kind 0 = Psi_n as "psi","chi","phi" (output_configuration),
+ * 1 = the assembled right-hand side under the same names (output_rhs; after pfc_assemble) [collective],
+ * 2 = the result of the last pfc_stress as tensor "stress" (output_stress).  mesh = what pfc_setup was given. */
+int pfc_output(pfc_handle *h, const pfc_mesh *mesh, int32_t kind, const char *directory, const char *basename,
+               uint32_t counter);
 /* the two Gram-Schmidt kernels at Krylov dimension dim (1..restart): multi-dot (reads dim+1
  * vectors) and multi-axpy with norm (reads dim+1, writes 1) */
 int pfc_time_krylov(pfc_handle *h, int32_t dim, int32_t reps, double *ms_dot, double *bytes_dot,

@@ -105,7 +105,7 @@ EXPORTED_SYMBOLS = [
     "pfc_nccl_unique_id", "pfc_comm_init", "pfc_comm_mode", "pfc_time_comm", "pfc_set_state", "pfc_get_state", "pfc_assemble",
     "pfc_residual_norm", "pfc_solve_update", "pfc_step", "pfc_run", "pfc_get_rhs", "pfc_get_nnz",
     "pfc_get_pattern", "pfc_get_matrix_values", "pfc_apply_operator", "pfc_get_dof_permutation",
-    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_stress", "pfc_standin_create",
+    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_stress", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
     "pfc_standin_create_ex", "pfc_standin_destroy",
     "pfc_standin_mesh", "pfc_standin_n_nodes", "pfc_standin_support_points",
     "pfc_standin_hexagonal_lattice", "pfc_plan_build", "pfc_plan_build_ex", "pfc_plan_get_lattice", "pfc_plan_get_view", "pfc_plan_monolithic",
@@ -178,6 +178,10 @@ def lib():
     L.pfc_time_precond.argtypes = [hp, C.c_int32, _f64p, _f64p]
     L.pfc_selfcheck.argtypes = [hp, _f64p]
     L.pfc_stress.argtypes = [hp, C.c_double, C.c_double, _f64p, C.POINTER(C.c_int64)]
+    L.pfc_vtu_write.argtypes = [C.POINTER(MeshStruct), C.c_char_p, C.c_char_p, C.c_uint32, C.c_int32, C.POINTER(C.c_char_p),
+                                _i32p, _f64p, C.c_char_p, C.c_int32]
+    L.pfc_vtu_piece_name.argtypes = [C.c_char_p, C.c_uint32, C.c_int32, C.c_int32, C.c_char_p, C.c_int32]
+    L.pfc_output.argtypes = [hp, C.POINTER(MeshStruct), C.c_int32, C.c_char_p, C.c_char_p, C.c_uint32]
     L.pfc_standin_create.argtypes = [C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double,
                                      C.c_int32, C.c_int32, C.POINTER(hp)]
     L.pfc_standin_create_ex.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_double,
@@ -212,6 +216,26 @@ def _p(a, ct):
 def default_A0(psi0: float, eps: float) -> float:
     """A_0 = "default" (app/simulations/phase_field_crystal_simulation_mpi.cpp:87-88)."""
     return 0.2 * (abs(psi0) + (1.0 / 3.0) * np.sqrt(-15 * eps - 36 * psi0 * psi0))
+
+
+def vtu_piece_name(basename, counter, rank, n_ranks):
+    buf = C.create_string_buffer(512)
+    if lib().pfc_vtu_piece_name(basename.encode(), counter, rank, n_ranks, buf, 512) != 0:
+        raise PfcError(1, "pfc_vtu_piece_name")
+    return buf.value.decode()
+
+
+def vtu_write(mesh, directory, basename, counter, names, values, interpretation=None):
+    """pfc_vtu_write: values [n_fields][N] nodal fields -> <directory><basename>_<counter>.<rank>.vtu (+ .pvtu on rank 0)."""
+    ptr = mesh.mesh_ptr if hasattr(mesh, "mesh_ptr") else mesh
+    v = np.ascontiguousarray(values, dtype=np.float64)
+    nm = (C.c_char_p * len(names))(*[n.encode() for n in names])
+    it = None if interpretation is None else np.ascontiguousarray(interpretation, dtype=np.int32)
+    err = C.create_string_buffer(400)
+    rc = lib().pfc_vtu_write(ptr, directory.encode(), basename.encode(), counter, len(names), nm,
+                             _p(it, C.c_int32) if it is not None else None, _p(v, C.c_double), err, 400)
+    if rc != 0:
+        raise PfcError(rc, err.value.decode())
 
 
 class StandIn:
@@ -450,6 +474,11 @@ class Solver:
         its = (C.c_int64 * 4)()
         self._check(lib().pfc_stress(self._h, eps, tol, _p(out, C.c_double), its))
         return out, list(its)
+
+    def output(self, mesh, kind, directory, basename, counter):
+        """kind 0: output_configuration (mpi.cpp:597-619), 1: output_rhs (:624-645), 2: output_stress (stress.cpp:358-384)."""
+        ptr = mesh.mesh_ptr if hasattr(mesh, "mesh_ptr") else mesh
+        self._check(lib().pfc_output(self._h, ptr, kind, directory.encode(), basename.encode(), counter))
 
     def time_precond(self, reps=10):
         ms, by = (C.c_double * 3)(), (C.c_double * 2)()

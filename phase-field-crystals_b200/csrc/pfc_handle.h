@@ -83,6 +83,7 @@ struct pfc_handle
   pfc::DevBuf<double> d_cell_h, d_tab;
   pfc::DevBuf<int64_t> d_slice_ptr, d_api_map, d_stress_map;
   pfc::DevBuf<double> d_stress, d_stress_io; // pfc_stress work fields (allocated on first use)
+  bool stress_valid = false;
   // matrix blocks (SELL entry order) and vectors
   pfc::DevBuf<double> d_B, d_C, d_M, d_K, d_rhs, d_psi_n, d_psi_n1, d_x, d_V, d_io;
   // Krylov control

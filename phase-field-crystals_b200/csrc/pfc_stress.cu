@@ -251,5 +251,70 @@ extern "C" int pfc_stress(pfc_handle *h, double eps, double tol, double *stress,
   PFC_CUDA(h, cudaGetLastError());
   PFC_CUDA(h, cudaMemcpyAsync(stress, h->d_stress_io.p, (size_t)4 * N * sizeof(double), cudaMemcpyDeviceToHost, s));
   PFC_CUDA(h, cudaStreamSynchronize(s));
+  h->stress_valid = true; // x (owned + ghost, distributed) stays in d_stress for pfc_output
+  return PFC_OK;
+}
+
+// ---- output: download owned + ghost values, hand them to the host VTU writer ----
+// kind 0: Psi_n as "psi", "chi", "phi" (output_configuration, mpi.cpp:597-619); 1: the assembled right-hand side under
+// the same names (output_rhs, mpi.cpp:624-645); 2: the result of the last pfc_stress as tensor "stress"
+// (StressCalculatorMPI::output_stress, stress.cpp:358-384).
+extern "C" int pfc_output(pfc_handle *h, const pfc_mesh *mesh, int32_t kind, const char *directory, const char *basename,
+                          uint32_t counter)
+{
+  if (!h || !mesh || !directory || !basename || kind < 0 || kind > 2)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->is_setup || (kind == 0 && !h->has_state))
+    return h->fail(PFC_ERR_STATE, "pfc_output needs pfc_setup and pfc_set_state first");
+  if (kind == 1 && !h->assembled)
+    return h->fail(PFC_ERR_STATE, "pfc_output(rhs) before pfc_assemble");
+  if (kind == 2 && !h->stress_valid)
+    return h->fail(PFC_ERR_STATE, "pfc_output(stress) before pfc_stress");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  const Plan &P = h->plan;
+  const int64_t N = P.n_dofs / 3, Np = P.Np, ss = (P.Np + P.n_ghost + 15) / 16 * 16;
+  if (mesh->block_size[0] != N || mesh->rank != P.rank || mesh->n_ranks != P.n_ranks)
+    return h->fail(PFC_ERR_BAD_ARGUMENT, "pfc_output: not the mesh pfc_setup was given");
+  const int nf = kind == 2 ? 4 : 3;
+  std::vector<double> values((size_t)nf * N, 0.0), dev;
+  if (kind == 2)
+    {
+      dev.resize((size_t)4 * ss);
+      PFC_CUDA(h, cudaMemcpyAsync(dev.data(), h->d_stress.p, dev.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+      PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+      for (int c = 0; c < 4; ++c)
+        {
+          for (int64_t r = 0; r < Np; ++r)
+            if (P.perm[r] >= 0)
+              values[c * N + P.perm[r]] = dev[c * ss + r];
+          for (int64_t g = 0; g < P.n_ghost; ++g)
+            values[c * N + P.ghost_global[g]] = dev[c * ss + Np + g];
+        }
+    }
+  else
+    {
+      double *src = kind == 0 ? h->d_psi_n.p : h->d_rhs.p;
+      if (kind == 1) // ghost rows of the right-hand side live on their owners
+        PFC_TRY(halo_exchange(h, src));
+      dev.resize((size_t)P.Lv);
+      PFC_CUDA(h, cudaMemcpyAsync(dev.data(), src, dev.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+      PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+      for (int c = 0; c < 3; ++c)
+        {
+          for (int64_t r = 0; r < Np; ++r)
+            if (P.perm[r] >= 0)
+              values[c * N + P.perm[r]] = dev[c * Np + r];
+          for (int64_t g = 0; g < P.n_ghost; ++g)
+            values[c * N + P.ghost_global[g]] = dev[3 * (Np + g) + c];
+        }
+    }
+  static const char *const state_names[3] = {"psi", "chi", "phi"};
+  static const char *const stress_names[4] = {"stress", "stress", "stress", "stress"};
+  static const int32_t scalar3[3] = {0, 0, 0}, tensor4[4] = {1, 1, 1, 1};
+  char err[400] = {0};
+  const int rc = pfc_vtu_write(mesh, directory, basename, counter, nf, kind == 2 ? stress_names : state_names,
+                               kind == 2 ? tensor4 : scalar3, values.data(), err, sizeof(err));
+  if (rc != PFC_OK)
+    return h->fail(rc, "%s", err);
   return PFC_OK;
 }

@@ -69,6 +69,31 @@ def main():
             err = np.abs(sg - o["stress"]).max() / np.abs(o["stress"]).max()
             print(f"[{world} ranks] stress: CG its gpu {its} oracle {o['cg_iters']} max rel diff {err:.2e}", flush=True)
             ok = ok and o["status"] == 0 and err <= 1e-8 and all(abs(a - b) <= 1 for a, b in zip(its, o["cg_iters"]))
+        # every rank writes its owned cells (ghost vertex values included), rank 0 the record
+        import tempfile
+        out = [tempfile.mkdtemp() + os.sep if rank == 0 else None]
+        dist.broadcast_object_list(out, src=0)
+        s.output(mesh, 0, out[0], "hexagonal_lattice", steps)
+        s.output(mesh, 2, out[0], "stress", 0)
+        dist.barrier()
+        if rank == 0:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            from vtu_reader import read_piece, read_record
+            key = {tuple(np.round(p, 9)): t for t, p in enumerate(om.support)}
+            rec = read_record(out[0] + f"hexagonal_lattice_{steps:02d}.pvtu")
+            ok = ok and len(rec["pieces"]) == world
+            n_cells, worst = 0, 0.0
+            for q in range(world):
+                pc = read_piece(out[0] + rec["pieces"][q])
+                ps = read_piece(out[0] + f"stress_00.{q}.vtu")
+                node = np.array([key[tuple(np.round(p[:2], 9))] for p in pc["points"]])
+                n_cells += pc["n_cells"]
+                for c, a in enumerate(("psi", "chi", "phi")):
+                    worst = max(worst, np.abs(pc["point_data"][a] - got[c * om.N + node]).max())
+                for c, slot in enumerate((0, 1, 3, 4)):
+                    worst = max(worst, np.abs(ps["point_data"]["stress"][:, slot] - sg[c, node]).max())
+            print(f"[{world} ranks] output: {n_cells} cells in {world} pieces, max |written - state| {worst:.2e}", flush=True)
+            ok = ok and n_cells == 4 ** n_refines and worst == 0.0
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, src=0)
     s.close()
