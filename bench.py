@@ -245,18 +245,22 @@ def main():
         t_wall = time.perf_counter() - t_wall0
     ms_dev = sum(s["ms_total"] for s in stats)
     launches = sum(s["kernel_launches"] for s in stats)
-    # ---- e2e: host buffers in, host buffers out, every step (state upload + step + psi download) ----
+    # ---- e2e: host buffers in, host buffers out, every step (state upload + step + state download) ----
+    # Every rank moves what a rank of the MPI original holds: its owned ranges of the three blocks
+    # (owned_partitioning, mpi.cpp:167-176; ghost values come over NVLink like update_ghost_values).
     # pinned ping-pong buffers: the state downloaded after step k is the state uploaded for step k + 1
     # (Psi_n_1 = Psi_n after a step, mpi.cpp:592)
-    outs = [torch.empty(n_dofs, dtype=torch.float64).pin_memory().numpy() for _ in range(2)]
-    outs[0][:] = start_state
+    n_own3 = 3 * solver.n_owned_nodes()
+    outs = [torch.empty(n_own3, dtype=torch.float64).pin_memory().numpy() for _ in range(2)]
+    solver.set_state(start_state, start_state)
+    solver.get_state_owned(out_n=outs[0])
     barrier()
     t0 = time.perf_counter()
     for k in range(args.steps):
         src, dst = outs[k & 1], outs[(k + 1) & 1]
-        solver.set_state(src, src)
+        solver.set_state_owned(src, src)
         st = solver.step()
-        solver.get_state(out_n=dst)
+        solver.get_state_owned(out_n=dst)
     barrier()
     t_e2e = time.perf_counter() - t0
 

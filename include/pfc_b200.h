@@ -162,6 +162,13 @@ int pfc_time_comm(pfc_handle *h, int32_t reps, double *ms3);
 /* ---- state (mpi.cpp:278-296 writes Psi_n, Psi_n_1; output reads them mpi.cpp:597-619) ---- */
 int pfc_set_state(pfc_handle *h, const double *Psi_n, const double *Psi_n_1); /* [n_dofs] each */
 int pfc_get_state(pfc_handle *h, double *Psi_n, double *Psi_n_1);             /* either may be NULL */
+/* The same with what a rank of the MPI original holds (owned_partitioning, mpi.cpp:167-176): arrays [3][n_owned],
+ * block b = the contiguous owned dofs block_start[b] + [node_offsets[rank], node_offsets[rank + 1]).
+ * pfc_set_state_owned fetches the ghost values from their owners (update_ghost_values) [collective];
+ * n_owned = pfc_n_owned_nodes.  Per-rank transfers are 24 n_owned bytes instead of 8 n_dofs. */
+int64_t pfc_n_owned_nodes(const pfc_handle *h);
+int pfc_set_state_owned(pfc_handle *h, const double *Psi_n, const double *Psi_n_1);
+int pfc_get_state_owned(pfc_handle *h, double *Psi_n, double *Psi_n_1);       /* either may be NULL */
 
 /* ---- the hot path ---------------------------------------------------------------------- */
 int pfc_assemble(pfc_handle *h);                        /* assemble_system, mpi.cpp:300-467 [collective] */

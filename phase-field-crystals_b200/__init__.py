@@ -102,7 +102,7 @@ class LatticeView(C.Structure):
 # every symbol include/pfc_b200.h declares (tests check the library exports all of them)
 EXPORTED_SYMBOLS = [
     "pfc_default_params", "pfc_create", "pfc_destroy", "pfc_last_error", "pfc_version", "pfc_setup",
-    "pfc_nccl_unique_id", "pfc_comm_init", "pfc_comm_mode", "pfc_time_comm", "pfc_set_state", "pfc_get_state", "pfc_assemble",
+    "pfc_nccl_unique_id", "pfc_comm_init", "pfc_comm_mode", "pfc_time_comm", "pfc_set_state", "pfc_get_state", "pfc_n_owned_nodes", "pfc_set_state_owned", "pfc_get_state_owned", "pfc_assemble",
     "pfc_residual_norm", "pfc_solve_update", "pfc_step", "pfc_run", "pfc_get_rhs", "pfc_get_nnz",
     "pfc_get_pattern", "pfc_get_matrix_values", "pfc_apply_operator", "pfc_get_dof_permutation",
     "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_stress", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
@@ -177,6 +177,10 @@ def lib():
     L.pfc_time_assembly.argtypes = [hp, C.c_int32, _f64p, _f64p]
     L.pfc_time_precond.argtypes = [hp, C.c_int32, _f64p, _f64p]
     L.pfc_selfcheck.argtypes = [hp, _f64p]
+    L.pfc_n_owned_nodes.argtypes = [hp]
+    L.pfc_n_owned_nodes.restype = C.c_int64
+    L.pfc_set_state_owned.argtypes = [hp, _f64p, _f64p]
+    L.pfc_get_state_owned.argtypes = [hp, _f64p, _f64p]
     L.pfc_stress.argtypes = [hp, C.c_double, C.c_double, _f64p, C.POINTER(C.c_int64)]
     L.pfc_vtu_write.argtypes = [C.POINTER(MeshStruct), C.c_char_p, C.c_char_p, C.c_uint32, C.c_int32, C.POINTER(C.c_char_p),
                                 _i32p, _f64p, C.c_char_p, C.c_int32]
@@ -406,6 +410,21 @@ class Solver:
         b = (np.empty(self.n_dofs) if out_n1 is None else out_n1) if (want_n1 or out_n1 is not None) else None
         self._check(lib().pfc_get_state(self._h, _p(a, C.c_double), _p(b, C.c_double) if b is not None else None))
         return (a, b) if b is not None else a
+
+    def n_owned_nodes(self):
+        return int(lib().pfc_n_owned_nodes(self._h))
+
+    def set_state_owned(self, Psi_n, Psi_n1):
+        """[3][n_owned] arrays (owned_partitioning, mpi.cpp:167-176); ghosts come from their owners."""
+        a = np.ascontiguousarray(Psi_n, dtype=np.float64)
+        b = a if Psi_n1 is Psi_n else np.ascontiguousarray(Psi_n1, dtype=np.float64)
+        assert a.size == 3 * self.n_owned_nodes() and b.size == a.size
+        self._check(lib().pfc_set_state_owned(self._h, _p(a, C.c_double), _p(b, C.c_double)))
+
+    def get_state_owned(self, out_n=None):
+        a = np.empty(3 * self.n_owned_nodes()) if out_n is None else out_n
+        self._check(lib().pfc_get_state_owned(self._h, _p(a, C.c_double), None))
+        return a
 
     def assemble(self):
         self._check(lib().pfc_assemble(self._h))

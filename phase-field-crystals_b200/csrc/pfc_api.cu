@@ -320,6 +320,80 @@ extern "C" int pfc_set_state(pfc_handle *h, const double *Psi_n, const double *P
   return PFC_OK;
 }
 
+// ---- owned-range transfers (multi-rank hosts hold only owned_partitioning, mpi.cpp:167-176) ----
+static int owned_map(pfc_handle *h)
+{
+  const Plan &P = h->plan;
+  if (h->d_owned_map.n == (size_t)(3 * P.n_owned))
+    return PFC_OK;
+  std::vector<int64_t> map((size_t)(3 * P.n_owned));
+  for (int c = 0; c < 3; ++c)
+    for (int64_t j = 0; j < P.n_owned; ++j)
+      map[c * P.n_owned + j] = c * P.Np + P.iperm[j];
+  PFC_CUDA(h, h->d_owned_map.upload(map, h->stream));
+  PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+  return PFC_OK;
+}
+
+extern "C" int64_t pfc_n_owned_nodes(const pfc_handle *h) { return (h && h->is_setup) ? h->plan.n_owned : -1; }
+
+extern "C" int pfc_set_state_owned(pfc_handle *h, const double *Psi_n, const double *Psi_n_1)
+{
+  if (!h || !Psi_n || !Psi_n_1)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->is_setup)
+    return h->fail(PFC_ERR_STATE, "pfc_set_state_owned before pfc_setup");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  int rc = owned_map(h);
+  if (rc != PFC_OK)
+    return rc;
+  const int64_t n = 3 * h->plan.n_owned;
+  const int blocks = (int)((n + 255) / 256);
+  const double *src[2] = {Psi_n, Psi_n_1};
+  double *dst[2] = {h->d_psi_n.p, h->d_psi_n1.p};
+  for (int k = 0; k < 2; ++k)
+    {
+      if (k == 0 || src[1] != src[0])
+        PFC_CUDA(h, cudaMemcpyAsync(h->d_io.p, src[k], n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+      scatter_kernel<<<blocks, 256, 0, h->stream>>>(dst[k], h->d_io.p, h->d_owned_map.p, n);
+      h->launches++;
+      rc = halo_exchange(h, dst[k]); // ghost values from their owners (update_ghost_values)
+      if (rc != PFC_OK)
+        return rc;
+    }
+  PFC_CUDA(h, cudaGetLastError());
+  PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+  h->has_state = true;
+  h->assembled = false;
+  return PFC_OK;
+}
+
+extern "C" int pfc_get_state_owned(pfc_handle *h, double *Psi_n, double *Psi_n_1)
+{
+  if (!h)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->is_setup || !h->has_state)
+    return h->fail(PFC_ERR_STATE, "pfc_get_state_owned before pfc_set_state");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  int rc = owned_map(h);
+  if (rc != PFC_OK)
+    return rc;
+  const int64_t n = 3 * h->plan.n_owned;
+  const int blocks = (int)((n + 255) / 256);
+  double *host[2] = {Psi_n, Psi_n_1};
+  const double *src[2] = {h->d_psi_n.p, h->d_psi_n1.p};
+  for (int k = 0; k < 2; ++k)
+    if (host[k])
+      {
+        gather_kernel<<<blocks, 256, 0, h->stream>>>(h->d_io.p, src[k], h->d_owned_map.p, n, 3 * h->plan.Np);
+        h->launches++;
+        PFC_CUDA(h, cudaMemcpyAsync(host[k], h->d_io.p, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+      }
+  PFC_CUDA(h, cudaGetLastError());
+  return PFC_OK;
+}
+
 static int download_vector(pfc_handle *h, const double *dvec, double *host)
 {
   const int64_t n = h->plan.n_dofs;

@@ -388,3 +388,17 @@ def test_output_writes_state_rhs_and_stress(built, tmp_path):
     for c, slot in enumerate((0, 1, 3, 4)):
         assert np.array_equal(t[:, slot], sg[c, node])
     s.close()
+
+
+def test_owned_range_state_transfers(built):
+    """pfc_set_state_owned / pfc_get_state_owned (what a rank of the MPI original holds); single rank: owned = all."""
+    om, st, s, Psi = _setup(built, 2, 3, operator_kind=1)
+    assert s.n_owned_nodes() == st.N
+    s.set_state_owned(Psi, Psi)
+    assert np.array_equal(s.get_state(), Psi) and np.array_equal(s.get_state_owned(), Psi)
+    a = s.step()
+    got = s.get_state_owned()
+    s.set_state(Psi, Psi)
+    b = s.step()
+    assert np.array_equal(got, s.get_state()) and a["gmres_iters"] == b["gmres_iters"]
+    s.close()
