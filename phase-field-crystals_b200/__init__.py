@@ -486,10 +486,11 @@ class Solver:
         self._check(lib().pfc_selfcheck(self._h, C.byref(v)))
         return v.value
 
-    def stress(self, eps, tol=1e-10):
+    def stress(self, eps, tol=1e-10, out=None):
         """StressCalculatorMPI::calculate_stress (stress_calculator_mpi.cpp:345-353) of the current Psi_n:
         ([4][N] nodal stress with c = a*2 + b, CG iterations per component)."""
-        out = np.zeros((4, self.n_dofs // 3))
+        if out is None:
+            out = np.zeros((4, self.n_dofs // 3))
         its = (C.c_int64 * 4)()
         self._check(lib().pfc_stress(self._h, eps, tol, _p(out, C.c_double), its))
         return out, list(its)

@@ -819,7 +819,8 @@ static __global__ void __launch_bounds__(kKsX) lat_kstencil_kernel(LatGeom L, La
 template <int P, int kKsX, int kKsY>
 static __global__ void __launch_bounds__(kKsX) lat_mass_kernel(LatGeom L, LatOp O)
 {
-  if (!((O.zmask >> blockIdx.z) & 1))
+  const int zmask = O.zmask_dev ? (O.zmask & *O.zmask_dev) : O.zmask;
+  if (!((zmask >> blockIdx.z) & 1))
     return;
   constexpr int R = kKsY + 2 * P;
   const int lx = blockIdx.x * kKsX + threadIdx.x, ly0 = blockIdx.y * kKsY;

@@ -40,6 +40,7 @@ struct LatOp
   int epi;
   int64_t zstride; // LAT_T / LAT_M: doubles between the batched scalar fields (tensor components)
   int zmask;       // LAT_M: bit c set = field c is processed
+  const int *zmask_dev; // LAT_M: if set, the mask is read from the device (and-ed with zmask)
 };
 
 

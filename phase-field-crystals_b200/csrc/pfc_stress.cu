@@ -29,9 +29,17 @@ using namespace pfc;
 
 namespace
 {
-struct Four
+// device-resident state of the batched CG: the host only polls it every few iterations
+struct StressCtl
 {
-  double v[4];
+  double gh[4];       // g_c . g_c of the previous iteration
+  double beta[4];
+  long long iters[4]; // SolverControl::last_step() per component
+  int mask;           // bit c set = component c still iterates
+  int it;
+  int fail;           // 1: max iterations, 2: non-finite
+  int fail_comp;
+  double fail_res;
 };
 
 // g = -b, d = b (b arrives in d), out[c] = b_c . b_c
@@ -51,11 +59,14 @@ __global__ void __launch_bounds__(kVecThreads) stress_init_kernel(double *__rest
   grid_reduce<4>(acc, partial, out, counter, ArDev{});
 }
 
-// out[c] = d_c . h_c for the components of mask
+// out[c] = d_c . h_c for the components still iterating
 __global__ void __launch_bounds__(kVecThreads) stress_dot_kernel(const double *__restrict__ d, const double *__restrict__ hh,
-                                                                 int64_t zstride, int64_t n, int mask, double *partial,
-                                                                 double *out, unsigned int *counter)
+                                                                 int64_t zstride, int64_t n, const StressCtl *ctl,
+                                                                 double *partial, double *out, unsigned int *counter)
 {
+  const int mask = ctl->mask;
+  if (!mask)
+    return;
   double acc[4] = {0, 0, 0, 0};
   for (int64_t i = (int64_t)blockIdx.x * kVecThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kVecThreads)
 #pragma unroll
@@ -69,13 +80,16 @@ __global__ void __launch_bounds__(kVecThreads) stress_dot_kernel(const double *_
 __global__ void __launch_bounds__(kVecThreads) stress_update_kernel(double *__restrict__ x, double *__restrict__ g,
                                                                     const double *__restrict__ d,
                                                                     const double *__restrict__ hh, int64_t zstride,
-                                                                    int64_t n, int mask, Four gh, const double *dh,
+                                                                    int64_t n, const StressCtl *ctl, const double *dh,
                                                                     double *partial, double *out, unsigned int *counter)
 {
+  const int mask = ctl->mask;
+  if (!mask)
+    return;
   double acc[4] = {0, 0, 0, 0}, alpha[4];
 #pragma unroll
   for (int c = 0; c < 4; ++c)
-    alpha[c] = ((mask >> c) & 1) ? gh.v[c] / dh[c] : 0.0;
+    alpha[c] = ((mask >> c) & 1) ? ctl->gh[c] / dh[c] : 0.0;
   for (int64_t i = (int64_t)blockIdx.x * kVecThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kVecThreads)
 #pragma unroll
     for (int c = 0; c < 4; ++c)
@@ -90,17 +104,64 @@ __global__ void __launch_bounds__(kVecThreads) stress_update_kernel(double *__re
   grid_reduce<4>(acc, partial, out, counter, ArDev{});
 }
 
+// SolverControl::check per component (stress_calculator_mpi.cpp:320, :329-334), then beta for the next direction
+__global__ void stress_ctl_kernel(StressCtl *ctl, const double *rr, double tol, long long max_iters, int first)
+{
+  if (first)
+    {
+      ctl->it = 0;
+      ctl->fail = 0;
+      ctl->mask = 0;
+    }
+  else if (!ctl->mask)
+    return;
+  else
+    ctl->it++;
+  const int it = ctl->it;
+  int mask = first ? 15 : ctl->mask;
+  for (int c = 0; c < 4; ++c)
+    {
+      if (!((mask >> c) & 1))
+        continue;
+      const double r2 = rr[c], res = sqrt(r2);
+      ctl->beta[c] = 0.0;
+      if (res <= tol)
+        {
+          ctl->iters[c] = it;
+          mask &= ~(1 << c);
+        }
+      else if (it >= max_iters || !isfinite(res))
+        {
+          ctl->fail = isfinite(res) ? 1 : 2;
+          ctl->fail_comp = c;
+          ctl->fail_res = res;
+          mask = 0;
+          break;
+        }
+      else
+        {
+          if (!first)
+            ctl->beta[c] = r2 / ctl->gh[c];
+          ctl->gh[c] = r2;
+        }
+    }
+  ctl->mask = mask;
+}
+
 // d_c = beta_c d_c - g_c
 __global__ void __launch_bounds__(kVecThreads) stress_dir_kernel(double *__restrict__ d, const double *__restrict__ g,
-                                                                 int64_t zstride, int64_t n, int mask, Four beta)
+                                                                 int64_t zstride, int64_t n, const StressCtl *ctl)
 {
+  const int mask = ctl->mask;
+  if (!mask)
+    return;
   for (int64_t i = (int64_t)blockIdx.x * kVecThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kVecThreads)
 #pragma unroll
     for (int c = 0; c < 4; ++c)
       if ((mask >> c) & 1)
         {
           const int64_t k = c * zstride + i;
-          d[k] = fma(beta.v[c], d[k], -g[k]);
+          d[k] = fma(ctl->beta[c], d[k], -g[k]);
         }
 }
 
@@ -115,15 +176,7 @@ __global__ void stress_distribute_kernel(double *v, const int32_t *slave, const 
     v[c * zstride + slave[k]] = v[c * zstride + master[k]];
 }
 
-int read4(pfc_handle *h, double *dev, double *host4)
-{
-  PFC_TRY(allreduce_sum(h, dev, 4));
-  PFC_CUDA(h, cudaMemcpyAsync(h->h_scalar, dev, 4 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-  PFC_CUDA(h, cudaStreamSynchronize(h->stream));
-  for (int c = 0; c < 4; ++c)
-    host4[c] = h->h_scalar[c];
-  return PFC_OK;
-}
+constexpr int kPollEvery = 8; // CG iterations between two looks at the control block
 } // namespace
 
 extern "C" int pfc_stress(pfc_handle *h, double eps, double tol, double *stress, int64_t *cg_iters)
@@ -140,9 +193,11 @@ extern "C" int pfc_stress(pfc_handle *h, double eps, double tol, double *stress,
   cudaStream_t s = h->stream;
   const int64_t ss = (P.Np + P.n_ghost + 15) / 16 * 16, Np = P.Np;
   const int64_t N = P.n_dofs / 3;
-  if (h->d_stress.n != (size_t)(16 * ss + 16))
+  constexpr int64_t kTail = 32; // doubles after the fields: dh[4], rr[4], StressCtl
+  static_assert(sizeof(StressCtl) <= (kTail - 8) * sizeof(double), "control block does not fit");
+  if (h->d_stress.n != (size_t)(16 * ss + kTail))
     {
-      PFC_CUDA(h, h->d_stress.alloc((size_t)(16 * ss + 16)));
+      PFC_CUDA(h, h->d_stress.alloc((size_t)(16 * ss + kTail)));
       // API node t -> address in a batched scalar field, owned nodes only (like pfc_get_state)
       std::vector<int64_t> map((size_t)4 * N, -1);
       for (int64_t r = 0; r < Np; ++r)
@@ -153,9 +208,11 @@ extern "C" int pfc_stress(pfc_handle *h, double eps, double tol, double *stress,
       PFC_CUDA(h, h->d_stress_io.alloc((size_t)4 * N));
       PFC_CUDA(h, cudaStreamSynchronize(s));
     }
+  h->stress_valid = false;
   double *x = h->d_stress.p, *g = x + 4 * ss, *d = x + 8 * ss, *hh = x + 12 * ss, *small = x + 16 * ss;
   double *dh = small, *rr = small + 4;
-  PFC_CUDA(h, cudaMemsetAsync(x, 0, (size_t)(16 * ss + 16) * sizeof(double), s));
+  StressCtl *ctl = reinterpret_cast<StressCtl *>(small + 8);
+  PFC_CUDA(h, cudaMemsetAsync(x, 0, (size_t)(16 * ss + kTail) * sizeof(double), s));
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((Np + kVecThreads - 1) / kVecThreads, 4 * (int64_t)h->n_sm));
 
   // right-hand side (all four components in one pass over the state), into d
@@ -168,73 +225,53 @@ extern "C" int pfc_stress(pfc_handle *h, double eps, double tol, double *stress,
     o.zstride = ss;
     PFC_TRY(lat_launch(h, LAT_T, o, nullptr));
   }
-  stress_init_kernel<<<grid, kVecThreads, 0, s>>>(g, d, ss, Np, h->d_partial.p, rr, h->d_counter.p);
-  h->launches++;
-  double r4[4], gh[4];
-  PFC_TRY(read4(h, rr, r4));
   // SolverControl(dof_handler.n_dofs()) of the dim*dim-component handler, default tolerance (stress.cpp:320)
-  const int64_t max_iters = 4 * (P.n_dofs / 3);
-  int mask = 0;
+  const long long max_iters = 4 * (long long)N;
+  stress_init_kernel<<<grid, kVecThreads, 0, s>>>(g, d, ss, Np, h->d_partial.p, rr, h->d_counter.p);
+  PFC_TRY(allreduce_sum(h, rr, 4));
+  stress_ctl_kernel<<<1, 1, 0, s>>>(ctl, rr, tol, max_iters, 1);
+  h->launches += 2;
+  StressCtl host{};
+  auto poll = [&]() -> int {
+    PFC_CUDA(h, cudaMemcpyAsync(&host, ctl, sizeof(StressCtl), cudaMemcpyDeviceToHost, s));
+    PFC_CUDA(h, cudaStreamSynchronize(s));
+    return PFC_OK;
+  };
+  PFC_TRY(poll());
+  while (host.mask && !host.fail)
+    {
+      // the host's mask is a superset of the device's (components only ever leave): exchange and launch for it,
+      // the kernels themselves follow the device mask
+      for (int k = 0; k < kPollEvery; ++k)
+        {
+          if (P.n_ranks > 1)
+            for (int c = 0; c < 4; ++c)
+              if ((host.mask >> c) & 1)
+                PFC_TRY(halo_exchange_scalar(h, d + c * ss));
+          LatOp o = lat_op(h);
+          o.s0 = d;
+          o.out = hh;
+          o.zstride = ss;
+          o.zmask = host.mask;
+          o.zmask_dev = &ctl->mask;
+          PFC_TRY(lat_launch(h, LAT_M, o, nullptr));
+          stress_dot_kernel<<<grid, kVecThreads, 0, s>>>(d, hh, ss, Np, ctl, h->d_partial.p, dh, h->d_counter.p);
+          PFC_TRY(allreduce_sum(h, dh, 4));
+          stress_update_kernel<<<grid, kVecThreads, 0, s>>>(x, g, d, hh, ss, Np, ctl, dh, h->d_partial.p, rr, h->d_counter.p);
+          PFC_TRY(allreduce_sum(h, rr, 4));
+          stress_ctl_kernel<<<1, 1, 0, s>>>(ctl, rr, tol, max_iters, 0);
+          stress_dir_kernel<<<grid, kVecThreads, 0, s>>>(d, g, ss, Np, ctl);
+          h->launches += 4;
+        }
+      PFC_TRY(poll());
+    }
+  if (host.fail == 2)
+    return h->fail(PFC_ERR_NONFINITE, "pfc_stress: non-finite residual (component %d)", host.fail_comp);
+  if (host.fail)
+    return h->fail(PFC_ERR_GMRES_NOT_CONVERGED, "pfc_stress: CG did not converge in %d iterations (component %d, residual %.3e)",
+                   host.it, host.fail_comp, host.fail_res);
   for (int c = 0; c < 4; ++c)
-    {
-      cg_iters[c] = 0;
-      gh[c] = r4[c];
-      if (!std::isfinite(r4[c]))
-        return h->fail(PFC_ERR_NONFINITE, "pfc_stress: non-finite right-hand side");
-      if (std::sqrt(r4[c]) > tol)
-        mask |= 1 << c;
-    }
-  int64_t it = 0;
-  while (mask)
-    {
-      ++it;
-      if (P.n_ranks > 1)
-        for (int c = 0; c < 4; ++c)
-          if ((mask >> c) & 1)
-            PFC_TRY(halo_exchange_scalar(h, d + c * ss));
-      {
-        LatOp o = lat_op(h);
-        o.s0 = d;
-        o.out = hh;
-        o.zstride = ss;
-        o.zmask = mask;
-        PFC_TRY(lat_launch(h, LAT_M, o, nullptr));
-      }
-      stress_dot_kernel<<<grid, kVecThreads, 0, s>>>(d, hh, ss, Np, mask, h->d_partial.p, dh, h->d_counter.p);
-      PFC_TRY(allreduce_sum(h, dh, 4));
-      Four ghv, beta;
-      for (int c = 0; c < 4; ++c)
-        ghv.v[c] = gh[c];
-      stress_update_kernel<<<grid, kVecThreads, 0, s>>>(x, g, d, hh, ss, Np, mask, ghv, dh, h->d_partial.p, rr,
-                                                       h->d_counter.p);
-      h->launches += 2;
-      PFC_TRY(read4(h, rr, r4));
-      for (int c = 0; c < 4; ++c)
-        {
-          beta.v[c] = 0.0;
-          if (!((mask >> c) & 1))
-            continue;
-          const double res = std::sqrt(r4[c]);
-          if (res <= tol)
-            {
-              cg_iters[c] = it;
-              mask &= ~(1 << c);
-            }
-          else if (it >= max_iters || !std::isfinite(res))
-            return h->fail(PFC_ERR_GMRES_NOT_CONVERGED, "pfc_stress: CG did not converge in %lld iterations (component %d, residual %.3e)",
-                           (long long)it, c, res);
-          else
-            {
-              beta.v[c] = r4[c] / gh[c];
-              gh[c] = r4[c];
-            }
-        }
-      if (mask)
-        {
-          stress_dir_kernel<<<grid, kVecThreads, 0, s>>>(d, g, ss, Np, mask, beta);
-          h->launches++;
-        }
-    }
+    cg_iters[c] = host.iters[c];
   // constraints.distribute, then the API order
   if (P.n_ranks > 1)
     for (int c = 0; c < 4; ++c)
