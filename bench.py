@@ -277,11 +277,11 @@ def main():
     comm_legs = solver.time_comm(reps=50) if world > 1 else None
     stress_leg = None
     if args.mf:  # SURVEY.md 8f-1 (outside the timed region): stress projection of the final state, result to the host
-        sbuf = torch.empty((4, n_dofs // 3), dtype=torch.float64).pin_memory().numpy()
-        solver.stress(EPS, out=sbuf)
+        sbuf = torch.empty((4, solver.n_owned_nodes()), dtype=torch.float64).pin_memory().numpy()
+        solver.stress(EPS, out=sbuf, owned=True)
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        _, cg_its = solver.stress(EPS, out=sbuf)
+        _, cg_its = solver.stress(EPS, out=sbuf, owned=True)
         stress_leg = {"ms_wall_incl_d2h": (time.perf_counter() - t0) * 1e3, "cg_iters": [int(i) for i in cg_its],
                       "d2h_bytes": int(sbuf.nbytes)}
     peak, peak_src = measured_peak()

@@ -213,6 +213,8 @@ int pfc_selfcheck(pfc_handle *h, double *max_rel);
  * PFC_ERR_UNSUPPORTED otherwise, PFC_ERR_GMRES_NOT_CONVERGED where the reference's SolverCG would throw
  * NoConvergence.  [collective] */
 int pfc_stress(pfc_handle *h, double eps, double tol, double *stress, int64_t *cg_iters);
+/* the same with stress [4][n_owned] over this rank's owned nodes (node_offsets[rank] + j), cf. pfc_get_state_owned */
+int pfc_stress_owned(pfc_handle *h, double eps, double tol, double *stress, int64_t *cg_iters);
 
 /* ---- output -----------------------------------------------------------------
  * Host-side writer replacing DataOut::build_patches() + write_vtu_with_pvtu_record(directory, basename,

@@ -105,7 +105,7 @@ EXPORTED_SYMBOLS = [
     "pfc_nccl_unique_id", "pfc_comm_init", "pfc_comm_mode", "pfc_time_comm", "pfc_set_state", "pfc_get_state", "pfc_n_owned_nodes", "pfc_set_state_owned", "pfc_get_state_owned", "pfc_assemble",
     "pfc_residual_norm", "pfc_solve_update", "pfc_step", "pfc_run", "pfc_get_rhs", "pfc_get_nnz",
     "pfc_get_pattern", "pfc_get_matrix_values", "pfc_apply_operator", "pfc_get_dof_permutation",
-    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_stress", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
+    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_stress", "pfc_stress_owned", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
     "pfc_standin_create_ex", "pfc_standin_destroy",
     "pfc_standin_mesh", "pfc_standin_n_nodes", "pfc_standin_support_points",
     "pfc_standin_hexagonal_lattice", "pfc_plan_build", "pfc_plan_build_ex", "pfc_plan_get_lattice", "pfc_plan_get_view", "pfc_plan_monolithic",
@@ -182,6 +182,7 @@ def lib():
     L.pfc_set_state_owned.argtypes = [hp, _f64p, _f64p]
     L.pfc_get_state_owned.argtypes = [hp, _f64p, _f64p]
     L.pfc_stress.argtypes = [hp, C.c_double, C.c_double, _f64p, C.POINTER(C.c_int64)]
+    L.pfc_stress_owned.argtypes = [hp, C.c_double, C.c_double, _f64p, C.POINTER(C.c_int64)]
     L.pfc_vtu_write.argtypes = [C.POINTER(MeshStruct), C.c_char_p, C.c_char_p, C.c_uint32, C.c_int32, C.POINTER(C.c_char_p),
                                 _i32p, _f64p, C.c_char_p, C.c_int32]
     L.pfc_vtu_piece_name.argtypes = [C.c_char_p, C.c_uint32, C.c_int32, C.c_int32, C.c_char_p, C.c_int32]
@@ -486,13 +487,14 @@ class Solver:
         self._check(lib().pfc_selfcheck(self._h, C.byref(v)))
         return v.value
 
-    def stress(self, eps, tol=1e-10, out=None):
+    def stress(self, eps, tol=1e-10, out=None, owned=False):
         """StressCalculatorMPI::calculate_stress (stress_calculator_mpi.cpp:345-353) of the current Psi_n:
-        ([4][N] nodal stress with c = a*2 + b, CG iterations per component)."""
+        ([4][N] nodal stress with c = a*2 + b — [4][n_owned] if owned —, CG iterations per component)."""
         if out is None:
-            out = np.zeros((4, self.n_dofs // 3))
+            out = np.zeros((4, self.n_owned_nodes() if owned else self.n_dofs // 3))
         its = (C.c_int64 * 4)()
-        self._check(lib().pfc_stress(self._h, eps, tol, _p(out, C.c_double), its))
+        f = lib().pfc_stress_owned if owned else lib().pfc_stress
+        self._check(f(self._h, eps, tol, _p(out, C.c_double), its))
         return out, list(its)
 
     def output(self, mesh, kind, directory, basename, counter):

@@ -179,7 +179,7 @@ __global__ void stress_distribute_kernel(double *v, const int32_t *slave, const 
 constexpr int kPollEvery = 8; // CG iterations between two looks at the control block
 } // namespace
 
-extern "C" int pfc_stress(pfc_handle *h, double eps, double tol, double *stress, int64_t *cg_iters)
+static int stress_impl(pfc_handle *h, double eps, double tol, double *stress, int64_t *cg_iters, bool owned)
 {
   if (!h || !stress || !cg_iters)
     return PFC_ERR_BAD_ARGUMENT;
@@ -198,15 +198,29 @@ extern "C" int pfc_stress(pfc_handle *h, double eps, double tol, double *stress,
   if (h->d_stress.n != (size_t)(16 * ss + kTail))
     {
       PFC_CUDA(h, h->d_stress.alloc((size_t)(16 * ss + kTail)));
-      // API node t -> address in a batched scalar field, owned nodes only (like pfc_get_state)
-      std::vector<int64_t> map((size_t)4 * N, -1);
-      for (int64_t r = 0; r < Np; ++r)
-        if (P.perm[r] >= 0)
+      h->stress_map_owned = -1;
+    }
+  const int64_t n_out = owned ? 4 * P.n_owned : 4 * N;
+  if (h->stress_map_owned != (owned ? 1 : 0))
+    {
+      // output position -> address in a batched scalar field; owned nodes only (like pfc_get_state):
+      // API order [4][N] by global node, or [4][n_owned] by owned node
+      std::vector<int64_t> map((size_t)n_out, -1);
+      if (owned)
+        {
           for (int c = 0; c < 4; ++c)
-            map[c * N + P.perm[r]] = c * ss + r;
+            for (int64_t j = 0; j < P.n_owned; ++j)
+              map[c * P.n_owned + j] = c * ss + P.iperm[j];
+        }
+      else
+        for (int64_t r = 0; r < Np; ++r)
+          if (P.perm[r] >= 0)
+            for (int c = 0; c < 4; ++c)
+              map[c * N + P.perm[r]] = c * ss + r;
       PFC_CUDA(h, h->d_stress_map.upload(map, s));
-      PFC_CUDA(h, h->d_stress_io.alloc((size_t)4 * N));
+      PFC_CUDA(h, h->d_stress_io.alloc((size_t)n_out));
       PFC_CUDA(h, cudaStreamSynchronize(s));
+      h->stress_map_owned = owned ? 1 : 0;
     }
   h->stress_valid = false;
   double *x = h->d_stress.p, *g = x + 4 * ss, *d = x + 8 * ss, *hh = x + 12 * ss, *small = x + 16 * ss;
@@ -282,14 +296,23 @@ extern "C" int pfc_stress(pfc_handle *h, double eps, double tol, double *stress,
       stress_distribute_kernel<<<(int)((nsl + 255) / 256), 256, 0, s>>>(x, h->d_slave.p, h->d_slave_master.p, nsl, ss);
       h->launches++;
     }
-  PFC_CUDA(h, cudaMemsetAsync(h->d_stress_io.p, 0, (size_t)4 * N * sizeof(double), s));
-  gather_kernel<<<(int)((4 * N + 255) / 256), 256, 0, s>>>(h->d_stress_io.p, x, h->d_stress_map.p, 4 * N, 4 * ss);
+  PFC_CUDA(h, cudaMemsetAsync(h->d_stress_io.p, 0, (size_t)n_out * sizeof(double), s));
+  gather_kernel<<<(int)((n_out + 255) / 256), 256, 0, s>>>(h->d_stress_io.p, x, h->d_stress_map.p, n_out, 4 * ss);
   h->launches++;
   PFC_CUDA(h, cudaGetLastError());
-  PFC_CUDA(h, cudaMemcpyAsync(stress, h->d_stress_io.p, (size_t)4 * N * sizeof(double), cudaMemcpyDeviceToHost, s));
+  PFC_CUDA(h, cudaMemcpyAsync(stress, h->d_stress_io.p, (size_t)n_out * sizeof(double), cudaMemcpyDeviceToHost, s));
   PFC_CUDA(h, cudaStreamSynchronize(s));
   h->stress_valid = true; // x (owned + ghost, distributed) stays in d_stress for pfc_output
   return PFC_OK;
+}
+
+extern "C" int pfc_stress(pfc_handle *h, double eps, double tol, double *stress, int64_t *cg_iters)
+{
+  return stress_impl(h, eps, tol, stress, cg_iters, false);
+}
+extern "C" int pfc_stress_owned(pfc_handle *h, double eps, double tol, double *stress, int64_t *cg_iters)
+{
+  return stress_impl(h, eps, tol, stress, cg_iters, true);
 }
 
 // ---- output: download owned + ghost values, hand them to the host VTU writer ----

@@ -85,6 +85,8 @@ def main():
         ref = om.newton_step(Pn, Pn1, 0.1, kw.get("theta", 1.0), -0.8)  # keep the oracle in step with the extra step
     if check_stress:  # stress projection of the stepped state, owned nodes summed over the ranks
         sg, its = s.stress(-0.8)
+        so, its_o = s.stress(-0.8, owned=True)  # the rank's slice of the same result
+        assert its_o == its and all(np.array_equal(so[c], sg[c, o0:o0 + no]) for c in range(4))
         mine = torch.from_numpy(sg).cuda()
         dist.all_reduce(mine)
         sg = mine.cpu().numpy()

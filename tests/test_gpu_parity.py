@@ -311,6 +311,8 @@ def test_stress_matches_oracle(built, degree, n_refines):
           f"max |diff| {np.abs(got - o['stress']).max():.2e} of {np.abs(o['stress']).max():.2e}")
     assert np.abs(got - o["stress"]).max() <= 1e-9 * np.abs(o["stress"]).max()
     assert all(abs(a - b) <= 1 for a, b in zip(its, o["cg_iters"]))
+    so, its_o = s.stress(EPS, owned=True)
+    assert np.array_equal(so, got) and its_o == its  # single rank: owned = all
     # off-diagonal components differ (div tau term), periodic images equal their masters
     assert np.abs(got[1] - got[2]).max() > 1e-3
     sl = np.nonzero(om.master[:om.N] >= 0)[0]
