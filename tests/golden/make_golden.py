@@ -29,7 +29,22 @@ def run(degree, n_refines, steps, disl, name):
     print(name, its)
 
 
+def run_stress(degree, n_refines, name_in, name_out):
+    """stress projection (stress_calculator_mpi.cpp:345-353) of a committed state, as the reference computes it after
+    every timestep (mpi.cpp:690-693)"""
+    om = O.Mesh(degree, n_refines, (-6 * A, -5 * A), (6 * A, 5 * A))
+    g = np.load(os.path.join(HERE, name_in))
+    r = om.stress(np.concatenate([g["psi"], g["chi"], g["phi"]]), -0.8)
+    assert r["status"] == 0
+    np.savez_compressed(os.path.join(HERE, name_out), stress=r["stress"], cg_iters=np.array(r["cg_iters"]))
+    print(name_out, r["cg_iters"])
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "stress":  # only the stress fixtures (the state fixtures stay as committed)
+        run_stress(1, 6, "config1_step1.npz", "config1_step1_stress.npz")
+        run_stress(2, 4, "q2_r4_step3.npz", "q2_r4_step3_stress.npz")
+        sys.exit(0)
     run(1, 6, 1, True, "config1_step1.npz")      # shipped TOML, first timestep
     run(1, 6, 10, True, "config1_step10.npz")    # shipped TOML, all 10 timesteps (n_timesteps = 10)
     run(2, 4, 3, True, "q2_r4_step3.npz")

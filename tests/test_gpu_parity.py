@@ -404,3 +404,22 @@ def test_owned_range_state_transfers(built):
     b = s.step()
     assert np.array_equal(got, s.get_state()) and a["gmres_iters"] == b["gmres_iters"]
     s.close()
+
+
+@pytest.mark.parametrize("name,degree,n_refines", [("config1_step1", 1, 6), ("q2_r4_step3", 2, 4)])
+def test_stress_against_committed_golden(built, name, degree, n_refines):
+    """pfc_stress of a committed state vs the committed oracle stress (tests/golden/make_golden.py stress), without
+    the oracle: config 1 = the shipped TOML after its first timestep, where the reference computes the stress too
+    (mpi.cpp:690-693)."""
+    import os
+    gd = os.path.join(os.path.dirname(__file__), "golden")
+    g, gs = np.load(os.path.join(gd, name + ".npz")), np.load(os.path.join(gd, name + "_stress.npz"))
+    st = built.StandIn(degree, n_refines, P1, P2)
+    s = built.Solver(degree=degree, operator_kind=1)
+    s.setup(st)
+    Psi = np.concatenate([g["psi"], g["chi"], g["phi"]])
+    s.set_state(Psi, Psi)
+    got, its = s.stress(EPS)
+    assert np.abs(got - gs["stress"]).max() <= 1e-9 * np.abs(gs["stress"]).max()
+    assert its == [int(i) for i in gs["cg_iters"]]
+    s.close()
