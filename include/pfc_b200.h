@@ -234,7 +234,8 @@ int pfc_vtu_write(const pfc_mesh *mesh, const char *directory, const char *basen
 /* file name of the piece of `rank` (rank < 0: of the .pvtu record), without directory */
 int pfc_vtu_piece_name(const char *basename, uint32_t counter, int32_t rank, int32_t n_ranks, char *out, int32_t outlen);
 /* download (owned + ghost values) and write: kind 0 = Psi_n as "psi","chi","phi" (output_configuration),
- * 1 = the assembled right-hand side under the same names (output_rhs; after pfc_assemble) [collective],
+ * 1 = the right-hand side of the last assembly under the same names (output_rhs; system_rhs as it stands after
+ * pfc_assemble / pfc_step) [collective],
  * 2 = the result of the last pfc_stress as tensor "stress" (output_stress).  mesh = what pfc_setup was given. */
 int pfc_output(pfc_handle *h, const pfc_mesh *mesh, int32_t kind, const char *directory, const char *basename,
                uint32_t counter);

@@ -84,6 +84,7 @@ struct pfc_handle
   pfc::DevBuf<int64_t> d_slice_ptr, d_api_map, d_stress_map, d_owned_map;
   pfc::DevBuf<double> d_stress, d_stress_io; // pfc_stress work fields (allocated on first use)
   bool stress_valid = false;
+  bool rhs_valid = false; // d_rhs holds the right-hand side of the last assembly (system_rhs as output_rhs sees it)
   int stress_map_owned = -1; // which output map d_stress_map holds (-1 none, 0 [4][N], 1 [4][n_owned])
   // matrix blocks (SELL entry order) and vectors
   pfc::DevBuf<double> d_B, d_C, d_M, d_K, d_rhs, d_psi_n, d_psi_n1, d_x, d_V, d_io;

@@ -395,7 +395,7 @@ extern "C" int pfc_assemble(pfc_handle *h)
     return h->fail(PFC_ERR_STATE, "pfc_assemble needs pfc_setup and pfc_set_state first");
   PFC_CUDA(h, cudaSetDevice(h->device));
   PFC_TRY(launch_assembly(h, false));
-  h->assembled = true;
+  h->assembled = h->rhs_valid = true;
   return PFC_OK;
 }
 
@@ -472,7 +472,7 @@ extern "C" int pfc_step(pfc_handle *h, pfc_step_stats *st)
     {
       PFC_CUDA(h, cudaEventRecord(h->ev[1], s));
       PFC_TRY(launch_assembly(h, false)); // mpi.cpp:582
-      h->assembled = true;
+      h->assembled = h->rhs_valid = true;
       PFC_TRY(residual_norm_async(h)); // mpi.cpp:584
       PFC_CUDA(h, cudaEventRecord(h->ev[2], s));
       PFC_CUDA(h, cudaStreamSynchronize(s));
@@ -623,7 +623,7 @@ extern "C" int pfc_time_assembly(pfc_handle *h, int32_t reps, double *ms_mean, d
   float ms;
   PFC_CUDA(h, cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]));
   *ms_mean = ms / reps;
-  h->assembled = true;
+  h->assembled = h->rhs_valid = true;
   if (bytes_per_launch)
     // B, C zeroed + written (read-modify-write counted once each way): 2 * 2 * 8 per entry;
     // state read 48 / node, rhs write 24 / node; per cell tables (gather, row, spos, pos, h)

@@ -326,8 +326,8 @@ extern "C" int pfc_output(pfc_handle *h, const pfc_mesh *mesh, int32_t kind, con
     return PFC_ERR_BAD_ARGUMENT;
   if (!h->is_setup || (kind == 0 && !h->has_state))
     return h->fail(PFC_ERR_STATE, "pfc_output needs pfc_setup and pfc_set_state first");
-  if (kind == 1 && !h->assembled)
-    return h->fail(PFC_ERR_STATE, "pfc_output(rhs) before pfc_assemble");
+  if (kind == 1 && !h->rhs_valid)
+    return h->fail(PFC_ERR_STATE, "pfc_output(rhs) before the first assembly");
   if (kind == 2 && !h->stress_valid)
     return h->fail(PFC_ERR_STATE, "pfc_output(stress) before pfc_stress");
   PFC_CUDA(h, cudaSetDevice(h->device));

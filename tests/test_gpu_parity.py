@@ -423,3 +423,42 @@ def test_stress_against_committed_golden(built, name, degree, n_refines):
     assert np.abs(got - gs["stress"]).max() <= 1e-9 * np.abs(gs["stress"]).max()
     assert its == [int(i) for i in gs["cg_iters"]]
     s.close()
+
+
+def test_shipped_toml_run_end_to_end(built, tmp_path):
+    """The shipped parameter file through the mirror of PhaseFieldCrystalSystemMPI::run (mpi.cpp:650-711), one timestep:
+    the configuration written to <data_folder>phase_field_01.0.vtu equals the committed oracle state after step 1
+    (tests/golden/config1_step1.npz, psi rel L2 <= 1e-9), stress and right-hand-side files are in place."""
+    import os
+    import tomllib
+    import pfc_b200.simulation as S
+    from test_simulation_cpu import SHIPPED
+    from vtu_reader import read_piece, read_record
+    tbl = tomllib.loads(SHIPPED)
+    tbl["data_folder"] = str(tmp_path) + os.sep
+    tbl["n_timesteps"], tbl["output_interval"] = 1, 1
+    lines = []
+    sim = S.parse_simulation_parameters(tbl, log=lines.append)
+    sim.run()
+    d = tbl["data_folder"]
+    for f in ("phase_field_00.0.vtu", "phase_field_00.pvtu", "phase_field_rhs_00.0.vtu", "phase_field_01.0.vtu",
+              "phase_field_rhs_01.0.vtu", "stress_00.0.vtu", "stress_00.pvtu"):
+        assert os.path.exists(d + f), f
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "config1_step1.npz"))
+    gs = np.load(os.path.join(os.path.dirname(__file__), "golden", "config1_step1_stress.npz"))
+    key = {tuple(np.round(p, 9)): t for t, p in enumerate(sim.mesh.support)}
+    pc = read_piece(d + "phase_field_01.0.vtu")
+    node = np.array([key[tuple(np.round(p[:2], 9))] for p in pc["points"]])
+    for name in ("psi", "chi", "phi"):
+        assert _rel(pc["point_data"][name], g[name][node]) <= 1e-9, name
+    ps = read_piece(d + "stress_00.0.vtu")["point_data"]["stress"]
+    for c, slot in enumerate((0, 1, 3, 4)):
+        assert np.abs(ps[:, slot] - gs["stress"][c, node]).max() <= 1e-8 * np.abs(gs["stress"]).max()
+    assert np.all(read_piece(d + "phase_field_rhs_00.0.vtu")["point_data"]["psi"] == 0)
+    assert read_record(d + "stress_00.pvtu")["arrays"] == {"stress": 9}
+    text = "\n".join(lines)
+    for s_ in ("Making grid!", "Initializing stress_calculator!", "Number of stress iterations: ", "Iterating timestep: 1",
+               "Residual is: ", "Number of iterations: ", "Outputting configuration!"):
+        assert s_ in text, s_
+    assert text.count("Number of stress iterations: ") == 4
+    sim.close()

@@ -1,0 +1,63 @@
+"""Parameter-file front end (app/simulations/phase_field_crystal_simulation_mpi.cpp:15-141) — host only."""
+import tomllib
+
+import numpy as np
+import pytest
+
+# the shipped parameter-files/hexagonal_lattice.toml, verbatim values
+SHIPPED = """
+dim = 2
+degree = 1
+data_folder = "./temp-data/"
+configuration_filename = "phase_field.vtu"
+rhs_filename = "phase_field_rhs.vtu"
+output_interval = 10
+eps = -0.8
+dt = 0.1
+n_timesteps = 10
+theta = 1.0
+simulation_tol = 1e-8
+simulation_max_iters = 200
+n_refines = 6
+p1 = [-6.0, -5.0]
+p2 = [6.0, 5.0]
+scale_by_lattice_constant = true
+psi_0 = -0.43
+A_0 = "default"
+dislocation_positions = [[2.0, 0.0], [-2.0, 0.0]]
+burgers_vectors = [[1.0, 0.0], [-1.0, 0.0]]
+"""
+
+
+def test_shipped_parameter_file(built):
+    import pfc_b200.simulation as S
+    sys_ = S.parse_simulation_parameters(tomllib.loads(SHIPPED))
+    a = 4 * np.pi / np.sqrt(3.0)
+    assert (sys_.degree, sys_.n_refines, sys_.n_timesteps, sys_.output_interval) == (1, 6, 10, 10)
+    assert np.allclose(sys_.lower_left, (-6 * a, -5 * a)) and np.allclose(sys_.upper_right, (6 * a, 5 * a))
+    ic = sys_.initial_condition
+    assert ic.A_0 == pytest.approx(0.24010818710676385, abs=1e-16) and ic.psi_0 == -0.43
+    assert np.allclose(ic.dislocation_positions, [[2 * a, 0], [-2 * a, 0]]) and np.allclose(ic.burgers_vectors, [[a, 0], [-a, 0]])
+    assert (sys_.configuration_stem, sys_.rhs_stem, sys_.data_folder) == ("phase_field", "phase_field_rhs", "./temp-data/")
+    assert sys_.solver_kw == {"operator_kind": 1, "preconditioner": 1}
+
+
+@pytest.mark.parametrize("drop,msg", [("degree", "No degree in parameter file"), ("data_folder", "No data folder in parameter file"),
+                                      ("n_refines", "No n_refines in parameter file"), ("p2", "p1 is not an array!"),
+                                      ("burgers_vectors", "Incorrect input for burgers vectors")])
+def test_missing_parameters_raise_like_the_reference(built, drop, msg):
+    import pfc_b200.simulation as S
+    tbl = tomllib.loads(SHIPPED)
+    del tbl[drop]
+    with pytest.raises(ValueError, match=msg):
+        S.parse_simulation_parameters(tbl)
+
+
+def test_bad_A0(built):
+    import pfc_b200.simulation as S
+    tbl = tomllib.loads(SHIPPED)
+    tbl["A_0"] = "auto"
+    with pytest.raises(ValueError, match="Incorrect input for A_0"):
+        S.parse_simulation_parameters(tbl)
+    tbl["A_0"] = 0.3
+    assert S.parse_simulation_parameters(tbl).initial_condition.A_0 == 0.3
