@@ -170,6 +170,10 @@ def parse_simulation_parameters(tbl, **kw):
     bur = [[float(c) * s for c in b] for b in tbl["burgers_vectors"]]
     assert abs(A_0 - default_A0(psi_0, vals["eps"])) < 1e-15 or tbl.get("A_0") != "default"
     ic = HexagonalLattice(A_0, psi_0, pos, bur)
+    # optional [gpu] table (not in the reference; its files have none and parse unchanged): pfc_params fields such as
+    # operator_kind, preconditioner, precond_sweeps, orthogonalization, use_cuda_graph, device
+    for k, v in dict(tbl.get("gpu", {})).items():
+        kw.setdefault(k, v)
     return PhaseFieldCrystalSystemMPI(vals["degree"], data_folder, configuration_filename, rhs_filename, output_interval,
                                       vals["eps"], vals["dt"], vals["n_timesteps"], vals["theta"], vals["simulation_tol"],
                                       vals["simulation_max_iters"], vals["n_refines"], p1, p2, ic, **kw)

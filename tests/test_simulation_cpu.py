@@ -61,3 +61,11 @@ def test_bad_A0(built):
         S.parse_simulation_parameters(tbl)
     tbl["A_0"] = 0.3
     assert S.parse_simulation_parameters(tbl).initial_condition.A_0 == 0.3
+
+
+def test_optional_gpu_table(built):
+    """Old files parse unchanged; an optional [gpu] table carries pfc_params fields."""
+    import pfc_b200.simulation as S
+    tbl = tomllib.loads(SHIPPED + '\n[gpu]\noperator_kind = 0\npreconditioner = 0\n')
+    assert S.parse_simulation_parameters(tbl).solver_kw == {"operator_kind": 0, "preconditioner": 0}
+    assert S.parse_simulation_parameters(tbl, preconditioner=1).solver_kw == {"operator_kind": 0, "preconditioner": 1}
