@@ -322,6 +322,15 @@ def main():
                                            "frac": bytes_asm / ms_asm / 1e6 / peak}},
             "clocks": clk.summary(),
         }
+        # dram traffic of the roofline kernel from the committed ncu capture of the same workload (None for other sizes)
+        try:
+            with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+                tr = json.load(f)["lat_kernel<LAT_J>" if args.mf else "spmv_sell_kernel"]
+            if args.degree == 2 and args.n_refines == 9 and world == 1:
+                line["roofline"]["traffic"] = tr["bytes_per_launch"]
+                line["roofline"]["traffic_source"] = tr["source"]
+        except (OSError, KeyError, ValueError):
+            pass
         if comm_legs is not None:
             line["comm_legs_us"] = comm_legs
         if stress_leg is not None:
