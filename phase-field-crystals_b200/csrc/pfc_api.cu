@@ -152,7 +152,10 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
   if (!h || !mesh)
     return PFC_ERR_BAD_ARGUMENT;
   PFC_CUDA(h, cudaSetDevice(h->device));
-  h->is_setup = h->has_state = h->assembled = h->rhs_valid = false;
+  h->is_setup = h->has_state = h->assembled = h->rhs_valid = h->stress_valid = false;
+  h->stress_map_owned = -1; // maps derived from the previous plan
+  h->d_owned_map.release();
+  h->d_stress.release();
   comm_p2p_destroy(h); // peers hold mappings of the arena that is about to be replaced
   if (mesh->n_ranks > 1 && (!h->comm || h->comm_size != mesh->n_ranks || h->comm_rank != mesh->rank))
     return h->fail(PFC_ERR_STATE, "pfc_comm_init must precede pfc_setup for n_ranks > 1 (same rank / n_ranks)");
