@@ -69,3 +69,35 @@ def test_optional_gpu_table(built):
     tbl = tomllib.loads(SHIPPED + '\n[gpu]\noperator_kind = 0\npreconditioner = 0\n')
     assert S.parse_simulation_parameters(tbl).solver_kw == {"operator_kind": 0, "preconditioner": 0}
     assert S.parse_simulation_parameters(tbl, preconditioner=1).solver_kw == {"operator_kind": 0, "preconditioner": 1}
+
+
+# ---- native driver phase-field-crystals_b200/pfc_sim (csrc/pfc_sim.cpp), host-only behaviour --------------------
+def _pfc_sim(built, tmp_path, text, *flags):
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(built.__file__), "pfc_sim")
+    f = tmp_path / "p.toml"
+    f.write_text(text)
+    return subprocess.run([exe, *flags, str(f)], capture_output=True, text=True, timeout=60)
+
+
+def test_pfc_sim_check_mode_parses_the_shipped_file(built, tmp_path):
+    r = _pfc_sim(built, tmp_path, "# This is a test parameter file\n" + SHIPPED + "\n# dislocation_positions = []\n", "--check")
+    assert r.returncode == 0, r.stderr
+    assert "degree 1 n_refines 6 n_timesteps 10 output_interval 10" in r.stdout
+    assert "A_0 0.24010818710676385 dislocations 2" in r.stdout
+    assert "p1 -43.531184741621232 -36.275987284684355" in r.stdout
+    assert "./temp-data/phase_field_NN.R.vtu ./temp-data/phase_field_rhs_NN.R.vtu" in r.stdout
+    assert "gpu operator_kind 1 preconditioner 1" in r.stdout
+    r = _pfc_sim(built, tmp_path, SHIPPED + "\n[gpu]\noperator_kind = 0\npreconditioner = 0\n", "--check")
+    assert "gpu operator_kind 0 preconditioner 0" in r.stdout
+
+
+def test_pfc_sim_errors_like_the_reference_main(built, tmp_path):
+    """app_mpi.cpp:143-183: a missing key is caught and printed, exit code 0; a file that does not parse returns 1."""
+    r = _pfc_sim(built, tmp_path, SHIPPED.replace("degree = 1", ""), "--check")
+    assert r.returncode == 0 and "Found error in program!" in r.stderr and "No degree in parameter file" in r.stderr
+    r = _pfc_sim(built, tmp_path, SHIPPED.replace('A_0 = "default"', 'A_0 = "auto"'), "--check")
+    assert r.returncode == 0 and "Incorrect input for A_0" in r.stderr
+    r = _pfc_sim(built, tmp_path, "dim = [2\n")
+    assert r.returncode == 1 and "Parsing failed" in r.stderr
