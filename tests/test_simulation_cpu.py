@@ -101,3 +101,20 @@ def test_pfc_sim_errors_like_the_reference_main(built, tmp_path):
     assert r.returncode == 0 and "Incorrect input for A_0" in r.stderr
     r = _pfc_sim(built, tmp_path, "dim = [2\n")
     assert r.returncode == 1 and "Parsing failed" in r.stderr
+
+
+def test_pfc_sim_reader_covers_the_toml_forms_of_the_reference_files(built, tmp_path):
+    """comments after values, multi-line arrays, integer-valued floats, empty arrays (the commented-out perfect-lattice
+    variant of the shipped file), numeric A_0."""
+    text = (SHIPPED.replace('dislocation_positions = [[2.0, 0.0], [-2.0, 0.0]]', 'dislocation_positions = []  # perfect lattice')
+            .replace('burgers_vectors = [[1.0, 0.0], [-1.0, 0.0]]', 'burgers_vectors = [\n]\n')
+            .replace('A_0 = "default"', 'A_0 = 0.25 # amplitude')
+            .replace('p1 = [-6.0, -5.0]', 'p1 = [\n  -6.0,   # x\n  -5.0,\n]')
+            .replace('n_refines = 6', 'n_refines = 7'))
+    r = _pfc_sim(built, tmp_path, text, "--check")
+    assert r.returncode == 0 and r.stderr == "", r.stderr
+    assert "n_refines 7" in r.stdout and "A_0 0.25 dislocations 0" in r.stdout and "p1 -43.531184741621232 -36.275987284684355" in r.stdout
+    # and the Python front end reads the same file the same way
+    import pfc_b200.simulation as S
+    s = S.parse_simulation_parameters(tomllib.loads(text))
+    assert s.n_refines == 7 and s.initial_condition.A_0 == 0.25 and s.initial_condition.dislocation_positions == []
