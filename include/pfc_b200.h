@@ -198,6 +198,9 @@ int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms3, double *bytes2);
 /* consistency of redundant kernel forms on a deterministic pseudo-random field (lattice path: K product as node
  * stencil vs cell quadrature); max_rel = max |a - b| / max |a|.  0 when the handle has no redundant form. [collective] */
 int pfc_selfcheck(pfc_handle *h, double *max_rel);
+/* EXPERIMENTAL (not yet run on a GPU): the one-kernel constant-coefficient Chebyshev sweep that
+ * PFC_SMOOTHER=1 selects on a single rank, compared with the composition of the K-stencil and mass-stencil kernels */
+int pfc_selfcheck_smoother(pfc_handle *h, double *max_rel);
 
 /* ---- stress projection ------------------------------------------------------
  * Replaces StressCalculatorMPI<dim>::calculate_stress(mpi_communicator, Psi_dof_handler, Psi, eps)

@@ -105,7 +105,7 @@ EXPORTED_SYMBOLS = [
     "pfc_nccl_unique_id", "pfc_comm_init", "pfc_comm_mode", "pfc_time_comm", "pfc_set_state", "pfc_get_state", "pfc_n_owned_nodes", "pfc_set_state_owned", "pfc_get_state_owned", "pfc_assemble",
     "pfc_residual_norm", "pfc_solve_update", "pfc_step", "pfc_run", "pfc_get_rhs", "pfc_get_nnz",
     "pfc_get_pattern", "pfc_get_matrix_values", "pfc_apply_operator", "pfc_get_dof_permutation",
-    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_stress", "pfc_stress_owned", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
+    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_selfcheck_smoother", "pfc_stress", "pfc_stress_owned", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
     "pfc_standin_create_ex", "pfc_standin_destroy",
     "pfc_standin_mesh", "pfc_standin_n_nodes", "pfc_standin_support_points",
     "pfc_standin_hexagonal_lattice", "pfc_plan_build", "pfc_plan_build_ex", "pfc_plan_get_lattice", "pfc_plan_get_view", "pfc_plan_monolithic",
@@ -177,6 +177,7 @@ def lib():
     L.pfc_time_assembly.argtypes = [hp, C.c_int32, _f64p, _f64p]
     L.pfc_time_precond.argtypes = [hp, C.c_int32, _f64p, _f64p]
     L.pfc_selfcheck.argtypes = [hp, _f64p]
+    L.pfc_selfcheck_smoother.argtypes = [hp, _f64p]
     L.pfc_n_owned_nodes.argtypes = [hp]
     L.pfc_n_owned_nodes.restype = C.c_int64
     L.pfc_set_state_owned.argtypes = [hp, _f64p, _f64p]
@@ -501,6 +502,11 @@ class Solver:
         """kind 0: output_configuration (mpi.cpp:597-619), 1: output_rhs (:624-645), 2: output_stress (stress.cpp:358-384)."""
         ptr = mesh.mesh_ptr if hasattr(mesh, "mesh_ptr") else mesh
         self._check(lib().pfc_output(self._h, ptr, kind, directory.encode(), basename.encode(), counter))
+
+    def selfcheck_smoother(self):
+        v = C.c_double()
+        self._check(lib().pfc_selfcheck_smoother(self._h, C.byref(v)))
+        return v.value
 
     def time_precond(self, reps=10):
         ms, by = (C.c_double * 3)(), (C.c_double * 2)()

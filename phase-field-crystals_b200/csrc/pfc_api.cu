@@ -279,6 +279,7 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
   h->is_setup = true;
   // iterate-independent blocks M and K, once (they are re-assembled every Newton iteration
   // upstream, mpi.cpp:435-443, with identical values); the lattice path stores no matrix at all
+  h->smoother_const = h->lat && P.n_ranks == 1 && getenv("PFC_SMOOTHER") && atoi(getenv("PFC_SMOOTHER")) == 1;
   rc = h->lat ? lat_setup(h) : launch_assembly(h, true);
   if (rc != PFC_OK)
     {

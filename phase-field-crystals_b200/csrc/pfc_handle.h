@@ -83,6 +83,7 @@ struct pfc_handle
   pfc::DevBuf<double> d_cell_h, d_tab;
   pfc::DevBuf<int64_t> d_slice_ptr, d_api_map, d_stress_map, d_owned_map;
   pfc::DevBuf<double> d_stress, d_stress_io; // pfc_stress work fields (allocated on first use)
+  bool smoother_const = false; // EXPERIMENTAL: PFC_SMOOTHER=1, single rank, lattice path (pfc_lattice_smooth.cuh)
   bool stress_valid = false;
   bool rhs_valid = false; // d_rhs holds the right-hand side of the last assembly (system_rhs as output_rhs sees it)
   int stress_map_owned = -1; // which output map d_stress_map holds (-1 none, 0 [4][N], 1 [4][n_owned])

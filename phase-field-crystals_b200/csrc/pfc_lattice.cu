@@ -7,6 +7,7 @@
 
 #include "pfc_handle.h"
 #include "pfc_lattice.cuh"
+#include "pfc_lattice_smooth.cuh"
 
 namespace pfc
 {
@@ -123,6 +124,20 @@ int lat_launch(pfc_handle *h, int mode, const LatOp &op, const Ctl *ctl)
   return h->fail(PFC_ERR_BAD_ARGUMENT, "lat_launch: unknown mode");
 }
 
+// EXPERIMENTAL (PFC_SMOOTHER=1): one constant-coefficient Chebyshev sweep in one kernel, single rank only
+int lat_smooth(pfc_handle *h, const SmoothOp &op, const Ctl *ctl)
+{
+  constexpr int TX = 64, TY = 16;
+  const LatGeom &G = h->lat_geom;
+  const dim3 grid((G.w + TX - 1) / TX, (G.h + TY - 1) / TY);
+  if (h->plan.degree == 1)
+    lat_smooth_kernel<1, TX, TY><<<grid, kSmoothThreads, lat_smooth_smem<1, TX, TY>(), h->stream>>>(G, op, ctl);
+  else
+    lat_smooth_kernel<2, TX, TY><<<grid, kSmoothThreads, lat_smooth_smem<2, TX, TY>(), h->stream>>>(G, op, ctl);
+  h->launches++;
+  return PFC_OK;
+}
+
 // nodes N = w h; every field is read once (the halo ring through L2) and every output written once
 double lat_bytes(const pfc_handle *h, int mode)
 {
@@ -233,3 +248,84 @@ int lat_setup(pfc_handle *h)
   return PFC_OK;
 }
 } // namespace pfc
+
+// S~ x by lat_smooth_kernel against the composition of the K-stencil and mass-stencil kernels (first thing to run on a GPU
+// when the experimental smoother is taken up: DESIGN.md §9 item 2).  Single rank.
+extern "C" int pfc_selfcheck_smoother(pfc_handle *h, double *max_rel)
+{
+  using namespace pfc;
+  if (!h || !max_rel)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->is_setup || !h->lat || h->plan.n_ranks != 1)
+    return h->fail(PFC_ERR_UNSUPPORTED, "pfc_selfcheck_smoother needs the lattice path on a single rank");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  const LatGeom &G = h->lat_geom;
+  const int64_t n = (int64_t)G.w * G.h, ss = (h->plan.Np + h->plan.n_ghost + 15) / 16 * 16;
+  const double bbar = 0.9, cbar = -0.3, dtth = h->prm.dt * h->prm.theta;
+  DevBuf<double> F, Gm, Kt2, aux;
+  PFC_CUDA(h, F.alloc((size_t)4 * ss));   // x, t1, t2, (unused)
+  PFC_CUDA(h, Gm.alloc((size_t)4 * ss));  // M x, M t1, M t2
+  PFC_CUDA(h, Kt2.alloc((size_t)ss));
+  PFC_CUDA(h, aux.alloc((size_t)4 * ss + 2)); // rhs = 0 | dinv = 1 | d = 0 | xout | cheb
+  std::vector<double> x((size_t)ss, 0.0), ones((size_t)ss, 1.0);
+  uint64_t st = 88172645463325252ull;
+  for (int64_t r = 0; r < n; ++r)
+    {
+      st ^= st << 13, st ^= st >> 7, st ^= st << 17;
+      x[r] = (double)(st >> 11) / 9007199254740992.0 - 0.5;
+    }
+  cudaStream_t s = h->stream;
+  PFC_CUDA(h, cudaMemsetAsync(F.p, 0, F.n * sizeof(double), s));
+  PFC_CUDA(h, cudaMemsetAsync(Gm.p, 0, Gm.n * sizeof(double), s));
+  PFC_CUDA(h, cudaMemsetAsync(aux.p, 0, aux.n * sizeof(double), s));
+  PFC_CUDA(h, cudaMemcpyAsync(F.p, x.data(), ss * sizeof(double), cudaMemcpyHostToDevice, s));
+  PFC_CUDA(h, cudaMemcpyAsync(aux.p + ss, ones.data(), ss * sizeof(double), cudaMemcpyHostToDevice, s));
+  const double cheb[2] = {0.0, 1.0};
+  PFC_CUDA(h, cudaMemcpyAsync(aux.p + 4 * ss, cheb, sizeof(cheb), cudaMemcpyHostToDevice, s));
+  auto kprod = [&](const double *in, double *out) { // out = (K in) M_L^-1
+    LatOp o = lat_op(h);
+    o.s0 = in;
+    o.k = 1.0;
+    o.out = out;
+    return lat_launch(h, LAT_K, o, nullptr);
+  };
+  int rc = kprod(F.p, F.p + ss);
+  if (rc == PFC_OK)
+    rc = kprod(F.p + ss, F.p + 2 * ss);
+  if (rc == PFC_OK)
+    rc = kprod(F.p + 2 * ss, Kt2.p);
+  if (rc != PFC_OK)
+    return rc;
+  {
+    LatOp o = lat_op(h);
+    o.s0 = F.p;
+    o.out = Gm.p;
+    o.zstride = ss;
+    o.zmask = 7;
+    rc = lat_launch(h, LAT_M, o, nullptr);
+    if (rc != PFC_OK)
+      return rc;
+  }
+  SmoothOp so{F.p, aux.p, aux.p + ss, aux.p + 4 * ss, aux.p + 2 * ss, aux.p + 3 * ss, bbar, cbar, dtth};
+  rc = lat_smooth(h, so, nullptr);
+  if (rc != PFC_OK)
+    return rc;
+  std::vector<double> gm((size_t)3 * ss), kt2((size_t)ss), iml((size_t)n), xo((size_t)ss);
+  PFC_CUDA(h, cudaMemcpyAsync(gm.data(), Gm.p, gm.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+  PFC_CUDA(h, cudaMemcpyAsync(kt2.data(), Kt2.p, kt2.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+  PFC_CUDA(h, cudaMemcpyAsync(iml.data(), h->d_inv_ml.p, iml.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+  PFC_CUDA(h, cudaMemcpyAsync(xo.data(), aux.p + 3 * ss, xo.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+  PFC_CUDA(h, cudaStreamSynchronize(s));
+  PFC_CUDA(h, cudaGetLastError());
+  double worst = 0, scale = 0;
+  for (int64_t r = 0; r < n; ++r)
+    {
+      const double ref = bbar * gm[r] - cbar * gm[ss + r] + dtth * (kt2[r] / iml[r] - 2.0 * gm[2 * ss + r]);
+      const double got = x[r] - xo[r]; // d = -(S~ x), xout = x + d
+      worst = std::max(worst, std::fabs(got - ref));
+      scale = std::max(scale, std::fabs(ref));
+    }
+  *max_rel = scale > 0 ? worst / scale : worst;
+  return PFC_OK;
+}
+

@@ -44,6 +44,15 @@ struct LatOp
 };
 
 
+// EXPERIMENTAL constant-coefficient Chebyshev sweep (pfc_lattice_smooth.cuh; PFC_SMOOTHER=1, single rank)
+struct SmoothOp
+{
+  const double *x, *rhs, *dinv, *cheb; // cheb[0] = coefficient of d, cheb[1] = coefficient of dinv * residual
+  double *d, *xout;
+  double bbar, cbar, dtth;
+};
+int lat_smooth(pfc_handle *h, const SmoothOp &op, const Ctl *ctl);
+
 // host side (pfc_lattice.cu)
 int lat_setup(pfc_handle *h);                                              // after build_plan: lut upload, inv_ml
 int lat_launch(pfc_handle *h, int mode, const LatOp &op, const Ctl *ctl);  // stream-ordered, graph-capturable

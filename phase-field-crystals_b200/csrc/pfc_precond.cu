@@ -264,6 +264,13 @@ int precond_apply(pfc_handle *h, const double *in, double *out, const Ctl *ctl)
   double *x = xa, *xn = xb;
   for (int i = 1; i < h->sweeps; ++i)
     {
+      if (h->smoother_const)
+        { // EXPERIMENTAL: the sweep on S~ = M + D M_L^-1 K M_L^-1 K in one kernel
+          const SmoothOp so{x, rhs, h->d_dinvB.p, h->d_cheb.p + 2 * i, d, xn, 1.0, 0.0, h->prm.dt * h->prm.theta};
+          PFC_TRY(lat_smooth(h, so, ctl));
+          std::swap(x, xn);
+          continue;
+        }
       PFC_TRY(halo_exchange_scalar(h, x, ctl));
       run_kmv(h, S, nb, nullptr, 0.0, x, 1.0, t1, nullptr, ctl);
       PFC_TRY(halo_exchange_scalar(h, t1, ctl));

@@ -462,3 +462,21 @@ def test_shipped_toml_run_end_to_end(built, tmp_path):
         assert s_ in text, s_
     assert text.count("Number of stress iterations: ") == 4
     sim.close()
+
+
+@pytest.mark.skipif(__import__("os").environ.get("PFC_SMOOTHER") != "1",
+                    reason="experimental one-kernel smoother (DESIGN.md §9 item 2): run with PFC_SMOOTHER=1")
+@pytest.mark.parametrize("degree,n_refines", [(1, 6), (2, 5), (2, 7)])
+def test_experimental_smoother(built, degree, n_refines):
+    """First thing to run when the constant-coefficient smoother is taken up: the tiled kernel against the composition of
+    the existing stencil kernels, then a step against the oracle (the smoother changes the preconditioner, not the answer)."""
+    om, st, s, Psi = _setup(built, degree, n_refines, operator_kind=1, preconditioner=1)
+    assert s.selfcheck_smoother() <= 1e-12
+    if n_refines <= 6:
+        s.set_state(Psi, Psi)
+        g = s.step()
+        Pn, Pn1 = Psi.copy(), Psi.copy()
+        o = om.newton_step(Pn, Pn1, DT, 1.0, EPS)
+        assert g["status"] == 0 and o["status"] == 0 and _rel(s.get_state()[:om.N], Pn[:om.N]) <= 1e-9
+        print(f"smoother Q{degree} 2^{n_refines}: gmres {g['gmres_iters']}")
+    s.close()
