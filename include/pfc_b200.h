@@ -268,6 +268,11 @@ const double *pfc_standin_support_points(const pfc_standin *s); /* [N][2], node 
 int  pfc_standin_hexagonal_lattice(const pfc_standin *s, double A0, double psi0, int32_t n_dislocations,
                                    const double *positions /*[n][2]*/, const double *burgers /*[n][2]*/,
                                    double *Psi);
+/* Polycrystalline initial condition for BASELINE.json config 4 (a harness extension: the reference has no such
+ * function): periodic Voronoi grains around seeds[n][2]; grain g is HexagonalLattice<dim>::value (no dislocations)
+ * rotated by alpha[g] and shifted by offset[g][2].  Bit-identical to the oracle's orc_polycrystal on the same inputs. */
+int  pfc_standin_polycrystal(const pfc_standin *s, double A0, double psi0, int32_t n_grains, const double *seeds /*[n][2]*/,
+                             const double *alpha /*[n]*/, const double *offset /*[n][2]*/, double *Psi);
 
 /* ---- host-only view of what pfc_setup derives (tests run it without a GPU) ------------------
  * The same code path pfc_setup uses: shared scalar pattern in SELL-32-sigma order, internal

@@ -60,6 +60,7 @@ def lib():
         L.orc_mesh_create.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double]
         L.orc_mesh_destroy.argtypes = [C.POINTER(_Mesh)]
         L.orc_initial_condition.argtypes = [C.POINTER(_Mesh), C.c_double, C.c_double, C.c_int, dp, dp, dp]
+        L.orc_polycrystal.argtypes = [C.POINTER(_Mesh), C.c_double, C.c_double, C.c_int, dp, dp, dp, dp]
         L.orc_assemble.argtypes = [C.POINTER(_Mesh), dp, dp, C.c_double, C.c_double, C.c_double, dp, dp,
                                    C.c_int, C.c_int]
         L.orc_spmv.argtypes = [C.POINTER(_Mesh), dp, dp, dp]
@@ -132,6 +133,15 @@ class Mesh:
         bur = np.ascontiguousarray(np.asarray(burgers, dtype=np.float64).reshape(-1, 2))
         Psi = np.empty(self.n_dofs)
         lib().orc_initial_condition(self._p, A0, psi0, len(pos), _dp(pos), _dp(bur), _dp(Psi))
+        return Psi
+
+    def polycrystal(self, A0, psi0, seeds, alpha, offset):
+        """harness extension (BASELINE.json config 4): periodic Voronoi grains of rotated hexagonal lattices"""
+        sd = np.ascontiguousarray(np.asarray(seeds, dtype=np.float64).reshape(-1, 2))
+        al = np.ascontiguousarray(np.asarray(alpha, dtype=np.float64).reshape(-1))
+        of = np.ascontiguousarray(np.asarray(offset, dtype=np.float64).reshape(-1, 2))
+        Psi = np.empty(self.n_dofs)
+        lib().orc_polycrystal(self._p, A0, psi0, len(al), _dp(sd), _dp(al), _dp(of), _dp(Psi))
         return Psi
 
     def assemble(self, Psi_n, Psi_n1, dt, theta, eps, threads=1, dead_work=False):

@@ -422,6 +422,48 @@ void orc_initial_condition(const orc_mesh *m, double A0, double psi0, int n_disl
 }
 
 /* ------------------------------------------------------------------------------------------
+ * Polycrystalline initial condition (harness extension for BASELINE.json config 4; the reference has
+ * no such function).  Grain g owns the periodic Voronoi cell of its seed (minimum-image distance on
+ * the box); inside it the field is hex.cpp:52-77's cos-sum without dislocations, evaluated in the
+ * grain's frame: p' = R(alpha_g)^T rho + o_g with rho the minimum-image displacement from the seed,
+ * i.e. the lattice of hexagonal_lattice_value rotated by alpha_g and shifted by o_g.  The seeds,
+ * angles and offsets come from the caller (numpy PCG64(12345) in the harness) so that this function
+ * and the stand-in's copy see identical inputs; ties go to the lowest grain index.
+ * ------------------------------------------------------------------------------------------ */
+void orc_polycrystal(const orc_mesh *m, double A0, double psi0, int n_grains, const double *seeds,
+                     const double *alpha, const double *offset, double *Psi)
+{
+  const double W = m->x1 - m->x0, H = m->y1 - m->y0;
+#pragma omp parallel for schedule(static)
+  for (int64_t t = 0; t < m->N; ++t)
+    {
+      const double px = m->support[2 * t], py = m->support[2 * t + 1];
+      int best = 0;
+      double bd = 0, bx = 0, by = 0;
+      for (int g = 0; g < n_grains; ++g)
+        {
+          double dx = px - seeds[2 * g], dy = py - seeds[2 * g + 1];
+          dx -= W * rint(dx / W);
+          dy -= H * rint(dy / H);
+          const double d2 = dx * dx + dy * dy;
+          if (g == 0 || d2 < bd)
+            {
+              best = g;
+              bd = d2;
+              bx = dx;
+              by = dy;
+            }
+        }
+      const double ca = cos(alpha[best]), sa = sin(alpha[best]);
+      const double qx = ca * bx + sa * by + offset[2 * best];
+      const double qy = ca * by - sa * bx + offset[2 * best + 1];
+      for (int c = 0; c < 3; ++c)
+        Psi[c * m->N + t] = hexagonal_lattice_value(qx, qy, c, A0, psi0, 0, NULL, NULL);
+    }
+  orc_distribute(m, Psi);
+}
+
+/* ------------------------------------------------------------------------------------------
  * Assembly.  mpi.cpp:300-467, loops kept literal (dense dofs_per_cell^2 incl. structural zeros).
  * ------------------------------------------------------------------------------------------ */
 static int64_t csr_find(const orc_mesh *m, int64_t row, int32_t col)

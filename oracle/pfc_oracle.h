@@ -61,6 +61,11 @@ void orc_initial_condition(const orc_mesh *m, double A0, double psi0, int n_disl
                            const double *disl_pos /*[n][2]*/, const double *burgers /*[n][2]*/,
                            double *Psi /*[n_dofs]*/);
 
+/* Polycrystal (harness extension, BASELINE.json config 4; not in the reference): periodic Voronoi grains around
+ * seeds[n][2], grain g = hex.cpp:52-77's cos-sum rotated by alpha[g] and shifted by offset[g][2]. */
+void orc_polycrystal(const orc_mesh *m, double A0, double psi0, int n_grains, const double *seeds,
+                     const double *alpha, const double *offset, double *Psi /*[n_dofs]*/);
+
 /* mpi.cpp:300-467.  values[nnz] and rhs[n_dofs] are overwritten.
  * threads <= 1: strict serial cell order (parity mode); > 1: 4-colour OpenMP (timed mode).
  * dead_work != 0 additionally accumulates local_preconditioner_matrix (mpi.cpp:446-448). */

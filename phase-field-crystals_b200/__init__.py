@@ -108,7 +108,7 @@ EXPORTED_SYMBOLS = [
     "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_selfcheck_smoother", "pfc_stress", "pfc_stress_owned", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
     "pfc_standin_create_ex", "pfc_standin_destroy",
     "pfc_standin_mesh", "pfc_standin_n_nodes", "pfc_standin_support_points",
-    "pfc_standin_hexagonal_lattice", "pfc_plan_build", "pfc_plan_build_ex", "pfc_plan_get_lattice", "pfc_plan_get_view", "pfc_plan_monolithic",
+    "pfc_standin_hexagonal_lattice", "pfc_standin_polycrystal", "pfc_plan_build", "pfc_plan_build_ex", "pfc_plan_get_lattice", "pfc_plan_get_view", "pfc_plan_monolithic",
     "pfc_plan_destroy",
 ]
 
@@ -202,6 +202,7 @@ def lib():
     L.pfc_standin_support_points.argtypes = [hp]
     L.pfc_standin_support_points.restype = _f64p
     L.pfc_standin_hexagonal_lattice.argtypes = [hp, C.c_double, C.c_double, C.c_int32, _f64p, _f64p, _f64p]
+    L.pfc_standin_polycrystal.argtypes = [hp, C.c_double, C.c_double, C.c_int32, _f64p, _f64p, _f64p, _f64p]
     L.pfc_plan_build.argtypes = [C.POINTER(MeshStruct), C.c_int32, C.POINTER(hp), C.c_char_p, C.c_int32]
     L.pfc_plan_build_ex.argtypes = [C.POINTER(MeshStruct), C.c_int32, C.c_int32, C.POINTER(hp), C.c_char_p, C.c_int32]
     L.pfc_plan_get_lattice.argtypes = [hp, C.POINTER(LatticeView)]
@@ -222,6 +223,17 @@ def _p(a, ct):
 def default_A0(psi0: float, eps: float) -> float:
     """A_0 = "default" (app/simulations/phase_field_crystal_simulation_mpi.cpp:87-88)."""
     return 0.2 * (abs(psi0) + (1.0 / 3.0) * np.sqrt(-15 * eps - 36 * psi0 * psi0))
+
+
+def polycrystal_grains(p1, p2, n_grains=64, seed=12345):
+    """Grain table of the config-4 workload (SURVEY.md 8d "M4"): numpy PCG64(seed) -> seeds uniform in the box,
+    rotation alpha_g in [0, pi/3), offset in [0, a)^2.  Returns (seeds [K][2], alpha [K], offset [K][2])."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    uv = rng.random((n_grains, 2))
+    seeds = np.array([p1[0], p1[1]]) + uv * np.array([p2[0] - p1[0], p2[1] - p1[1]])
+    alpha = rng.random(n_grains) * (np.pi / 3.0)
+    offset = rng.random((n_grains, 2)) * LATTICE_A
+    return seeds, alpha, offset
 
 
 def vtu_piece_name(basename, counter, rank, n_ranks):
@@ -280,6 +292,19 @@ class StandIn:
                                                  _p(bur, C.c_double), _p(Psi, C.c_double))
         if rc != PFC_OK:
             raise PfcError(rc, "pfc_standin_hexagonal_lattice")
+        return Psi
+
+    def polycrystal(self, A0, psi0, seeds, alpha, offset):
+        """pfc_standin_polycrystal: periodic Voronoi grains, grain g = the hexagonal lattice rotated by alpha[g]."""
+        sd = np.ascontiguousarray(np.asarray(seeds, dtype=np.float64).reshape(-1, 2))
+        al = np.ascontiguousarray(np.asarray(alpha, dtype=np.float64).reshape(-1))
+        of = np.ascontiguousarray(np.asarray(offset, dtype=np.float64).reshape(-1, 2))
+        assert len(sd) == len(al) == len(of)
+        Psi = np.empty(self.n_dofs)
+        rc = lib().pfc_standin_polycrystal(self._h, A0, psi0, len(al), _p(sd, C.c_double), _p(al, C.c_double),
+                                           _p(of, C.c_double), _p(Psi, C.c_double))
+        if rc != PFC_OK:
+            raise PfcError(rc, "pfc_standin_polycrystal")
         return Psi
 
     def close(self):

@@ -26,6 +26,7 @@ struct pfc_standin
   pfc_mesh mesh;
   int degree, n_refines;
   int64_t N;
+  double x0, y0, x1, y1;
   std::vector<double> cell_vertices, support, shape, dshape, qw;
   std::vector<int32_t> cell_dofs, local_comp, local_shape, c_slave, c_master;
   std::vector<int64_t> node_offsets;
@@ -127,6 +128,7 @@ extern "C" int pfc_standin_create_ex(int32_t degree, int32_t n_refines, int32_t 
   S->degree = p;
   S->n_refines = n_refines;
   S->N = N;
+  S->x0 = x0, S->y0 = y0, S->x1 = x1, S->y1 = y1;
   const double hx = (x1 - x0) / nx, hy = (y1 - y0) / ny;
 
   // FE_Q(p) hierarchical local nodes as fine-grid offsets
@@ -373,6 +375,56 @@ extern "C" int pfc_standin_hexagonal_lattice(const pfc_standin *s, double A0, do
             }
           sum += std::cos((q[n][0] * px + q[n][1] * py) - phase);
         }
+      Psi[t] = psi0 + A0 * sum;
+      Psi[N + t] = -A0 * sum;
+      Psi[2 * N + t] = A0 * sum;
+    }
+  for (int c = 0; c < 3; ++c)
+    for (int64_t t = 0; t < N; ++t)
+      if (s->node_master[t] != t)
+        Psi[c * N + t] = Psi[c * N + s->node_master[t]];
+  return PFC_OK;
+}
+
+// Polycrystalline initial condition (harness extension for BASELINE.json config 4, not in the reference): periodic
+// Voronoi grains (minimum-image distance to seeds[n][2], ties to the lowest index); grain g carries the cos-sum of
+// HexagonalLattice<dim>::value (hexagonal_lattice.cpp:52-77, no dislocations) in its own frame
+// p' = R(alpha_g)^T rho + o_g, rho = minimum-image displacement from the seed.  Same operations in the same order as
+// orc_polycrystal (oracle/pfc_oracle.c): the two are compared bit for bit (tests/test_plan_cpu.py).
+extern "C" int pfc_standin_polycrystal(const pfc_standin *s, double A0, double psi0, int32_t n_grains, const double *seeds,
+                                       const double *alpha, const double *offset, double *Psi)
+{
+  if (!s || !Psi || n_grains < 1 || !seeds || !alpha || !offset)
+    return PFC_ERR_BAD_ARGUMENT;
+  const int64_t N = s->N;
+  const double W = s->x1 - s->x0, H = s->y1 - s->y0;
+  const double q[3][2] = {{0.0, 1.0}, {0.5 * std::sqrt(3.0), -0.5}, {-0.5 * std::sqrt(3.0), -0.5}};
+#pragma omp parallel for schedule(static)
+  for (int64_t t = 0; t < N; ++t)
+    {
+      const double px = s->support[2 * t], py = s->support[2 * t + 1];
+      int best = 0;
+      double bd = 0, bx = 0, by = 0;
+      for (int g = 0; g < n_grains; ++g)
+        {
+          double dx = px - seeds[2 * g], dy = py - seeds[2 * g + 1];
+          dx -= W * std::rint(dx / W);
+          dy -= H * std::rint(dy / H);
+          const double d2 = dx * dx + dy * dy;
+          if (g == 0 || d2 < bd)
+            {
+              best = g;
+              bd = d2;
+              bx = dx;
+              by = dy;
+            }
+        }
+      const double ca = std::cos(alpha[best]), sa = std::sin(alpha[best]);
+      const double qx = ca * bx + sa * by + offset[2 * best];
+      const double qy = ca * by - sa * bx + offset[2 * best + 1];
+      double sum = 0;
+      for (int n = 0; n < 3; ++n)
+        sum += std::cos((q[n][0] * qx + q[n][1] * qy) - 0.0);
       Psi[t] = psi0 + A0 * sum;
       Psi[N + t] = -A0 * sum;
       Psi[2 * N + t] = A0 * sum;

@@ -46,6 +46,42 @@ def test_standin_matches_oracle_bit_exact(built, degree, n_refines):
     assert np.array_equal(Psi, om.initial_condition(A0, PSI0, DISL, BURG))
 
 
+@pytest.mark.parametrize("degree,n_refines,n_grains", [(1, 5, 1), (1, 6, 7), (2, 4, 64), (2, 5, 5)])
+def test_polycrystal_standin_matches_oracle_bit_exact(built, degree, n_refines, n_grains):
+    """config-4 initial condition (harness extension): the stand-in's and the oracle's generators agree bit for bit,
+    grains are periodic Voronoi cells, every grain is the reference's cos-sum in a rotated frame."""
+    import oracle as O
+    om = O.Mesh(degree, n_refines, P1, P2)
+    st = built.StandIn(degree, n_refines, P1, P2)
+    A0 = built.default_A0(PSI0, EPS)
+    seeds, alpha, offset = built.polycrystal_grains(P1, P2, n_grains)
+    assert np.array_equal(built.polycrystal_grains(P1, P2, n_grains)[0], seeds)  # deterministic (PCG64 seed 12345)
+    assert 0 <= alpha.min() and alpha.max() < np.pi / 3 and seeds.shape == (n_grains, 2)
+    a = st.polycrystal(A0, PSI0, seeds, alpha, offset)
+    b = om.polycrystal(A0, PSI0, seeds, alpha, offset)
+    assert np.array_equal(a, b)
+    N = om.N
+    assert np.array_equal(a[N:2 * N], -(a[:N] - PSI0)) or np.allclose(a[N:2 * N], -(a[:N] - PSI0), atol=1e-15)
+    assert np.array_equal(a[2 * N:], -a[N:2 * N])
+    slaves = np.nonzero(om.master >= 0)[0]
+    assert np.array_equal(a[slaves], a[om.master[slaves]])  # constraints.distribute
+    # independent numpy evaluation of the definition
+    W, H = P2[0] - P1[0], P2[1] - P1[1]
+    d = om.support[:, None, :] - seeds[None, :, :]
+    d[..., 0] -= W * np.rint(d[..., 0] / W)
+    d[..., 1] -= H * np.rint(d[..., 1] / H)
+    g = np.argmin((d ** 2).sum(-1), axis=1)
+    rho = d[np.arange(N), g]
+    ca, sa = np.cos(alpha[g]), np.sin(alpha[g])
+    qx, qy = ca * rho[:, 0] + sa * rho[:, 1] + offset[g, 0], ca * rho[:, 1] - sa * rho[:, 0] + offset[g, 1]
+    ssum = np.cos(qy) + np.cos(0.5 * np.sqrt(3.0) * qx - 0.5 * qy) + np.cos(-0.5 * np.sqrt(3.0) * qx - 0.5 * qy)
+    free = om.master[:N] < 0
+    assert np.abs((PSI0 + A0 * ssum)[free] - a[:N][free]).max() <= 1e-12
+    if n_grains == 1:  # one grain with alpha = 0, offset 0 is the perfect lattice seen from the seed
+        z = st.polycrystal(A0, PSI0, [[0.0, 0.0]], [0.0], [[0.0, 0.0]])
+        assert np.abs(z - st.hexagonal_lattice(A0, PSI0))[:N][free].max() <= 1e-10
+
+
 @pytest.mark.parametrize("degree,n_refines", [(1, 1), (1, 2), (1, 5), (2, 1), (2, 3)])
 def test_pattern_bit_exact(built, degree, n_refines):
     om, st, _, _ = _case(built, degree, n_refines)
