@@ -586,12 +586,15 @@ extern "C" int pfc_time_operator(pfc_handle *h, int32_t reps, double *ms_mean, d
     return h->fail(PFC_ERR_STATE, "pfc_time_operator before pfc_assemble");
   PFC_CUDA(h, cudaSetDevice(h->device));
   const Plan &P = h->plan;
-  double *vx = h->d_V.p, *vy = h->d_V.p + h->stride;
+  // operands rotate through the Krylov basis (what the solver does), so that x and y do not stay in L2 between launches
+  const int half = std::max(1, h->n_basis / 2);
+  auto vx = [&](int i) { return h->d_V.p + (int64_t)(i % half) * h->stride; };
+  auto vy = [&](int i) { return h->d_V.p + (int64_t)(half + i % half) * h->stride; };
   for (int i = 0; i < 3; ++i)
-    PFC_TRY(apply_operator(h, vx, vy, nullptr));
+    PFC_TRY(apply_operator(h, vx(i), vy(i), nullptr));
   PFC_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
   for (int i = 0; i < reps; ++i)
-    PFC_TRY(apply_operator(h, vx, vy, nullptr));
+    PFC_TRY(apply_operator(h, vx(i), vy(i), nullptr));
   PFC_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
   PFC_CUDA(h, cudaStreamSynchronize(h->stream));
   float ms;

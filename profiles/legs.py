@@ -20,7 +20,7 @@ def main():
     ap.add_argument("--sweeps", type=int, nargs="*", default=[4])
     ap.add_argument("--steps", type=int, default=3)
     a = ap.parse_args()
-    _, p1, p2 = B.workload(a.degree, a.n_refines, 1)
+    _, p1, p2 = B.box(a.degree, a.n_refines)
     mesh = P.StandIn(a.degree, a.n_refines, p1, p2)
     Psi0 = mesh.hexagonal_lattice(P.default_A0(B.PSI0, B.EPS), B.PSI0)
     for sw in a.sweeps:

@@ -70,7 +70,7 @@ def test_gmres_solve_matches_oracle(built, degree, n_refines):
     # both solves stop at ||b - A x|| <= 1e-10 absolute: compare through the operator
     assert np.linalg.norm(om.spmv(ovals, np.where(om.master >= 0, 0.0, got)) - orhs) <= 2e-10
     assert _rel(got, xo) <= 1e-8
-    assert abs(its - oits) <= max(3, oits // 20), (its, oits)
+    assert its == oits, (its, oits)  # unpreconditioned: the same Krylov space, the same stopping decisions
     s.close()
 
 
@@ -479,4 +479,68 @@ def test_experimental_smoother(built, degree, n_refines):
         o = om.newton_step(Pn, Pn1, DT, 1.0, EPS)
         assert g["status"] == 0 and o["status"] == 0 and _rel(s.get_state()[:om.N], Pn[:om.N]) <= 1e-9
         print(f"smoother Q{degree} 2^{n_refines}: gmres {g['gmres_iters']}")
+    s.close()
+
+
+# ---- parity at the sizes the bench lines are quoted on (VERDICT r01 "what's weak" 2) -------------------
+def _bench_case(built, name):
+    import bench as B
+    import oracle as O
+    O.set_threads(B.host_cores())
+    wl = dict(B.WORKLOADS[name], name=name, custom=False)
+    S, p1, p2 = B.box(wl["degree"], wl["n_refines"])
+    A0 = built.default_A0(PSI0, EPS)
+    st = built.StandIn(wl["degree"], wl["n_refines"], p1, p2)
+    om = O.Mesh(wl["degree"], wl["n_refines"], p1, p2)
+    Psi = B.initial_condition(st, wl, p1, p2, S, A0)
+    assert np.array_equal(Psi, B.initial_condition(om, wl, p1, p2, S, A0))  # the two generators agree bit for bit
+    return B, wl, st, om, Psi
+
+
+@pytest.mark.parametrize("name", ["M2", "M4"])
+def test_bench_size_rhs_and_operator_match_oracle(built, name):
+    """-R and J x (random x) at the full bench size against the oracle's assembled monolithic CSR matrix, on the
+    matrix-free lattice path and on the assembled SELL path: grids of thousands of CTAs, ring / lut handling at tile
+    counts the small cases never reach.  Perturbed state so that Psi_n != Psi_n-1."""
+    B, wl, st, om, Psi = _bench_case(built, name)
+    N = om.N
+    Psi1 = Psi + 1e-2 * np.random.default_rng(7).standard_normal(Psi.size)
+    om.distribute(Psi1)
+    ovals, orhs = om.assemble(Psi1, Psi, DT, 1.0, EPS, threads=B.host_cores())
+    x = np.random.default_rng(3).standard_normal(3 * N)
+    ref = om.spmv(ovals, x)
+    free = om.master < 0
+    for kw in ({"operator_kind": 1, "preconditioner": 1}, {"operator_kind": 0}):
+        s = built.Solver(degree=wl["degree"], **kw)
+        s.setup(st)
+        s.set_state(Psi1, Psi)
+        s.assemble()
+        rhs = s.get_rhs()
+        e_rhs = np.abs(rhs - orhs).max() / np.abs(orhs).max()
+        y = s.apply_operator(x)
+        e_op = np.abs(y - ref)[free].max() / np.abs(ref).max()
+        e_nrm = abs(s.residual_norm() - np.linalg.norm(orhs)) / np.linalg.norm(orhs)
+        print(f"{name} {kw}: -R max rel {e_rhs:.2e}, J x max rel {e_op:.2e}, ||R|| rel {e_nrm:.2e}")
+        assert np.all(rhs[~free] == 0.0)
+        assert e_rhs <= 1e-12 and e_op <= 1e-12 and e_nrm <= 1e-12
+        s.close()
+
+
+def test_bench_size_step_matches_oracle_M2(built):
+    """psi after one time step at M2 (Q2 2^9, 3.15 M DoF): bench path (lattice kernels + block-Schur preconditioner)
+    against the oracle's unpreconditioned reference algorithm (about 20 s of CPU)."""
+    B, wl, st, om, Psi = _bench_case(built, "M2")
+    N = om.N
+    s = built.Solver(degree=2, operator_kind=1, preconditioner=1)
+    s.setup(st)
+    s.set_state(Psi, Psi)
+    g = s.step()
+    got = s.get_state()
+    Pn, Pn1 = Psi.copy(), Psi.copy()
+    o = om.newton_step(Pn, Pn1, DT, 1.0, EPS, threads=B.host_cores())
+    err = _rel(got[:N], Pn[:N])
+    print(f"M2 step 1: newton gpu {g['residuals']} oracle {o['residuals']}; gmres gpu {g['gmres_iters']} oracle {o['gmres_iters']}; "
+          f"rel L2 psi {err:.2e}")
+    assert g["status"] == 0 and o["status"] == 0 and g["n_assemblies"] == o["n_assemblies"]
+    assert err <= 1e-9 and _rel(got, Pn) <= 1e-9
     s.close()
