@@ -276,8 +276,15 @@ def kernel_legs(solver, stats, sweeps, precond, mf, peak, n_nodes, ms_per_step):
     if precond:
         pc = solver.time_precond(reps=20)
         n_pc = n_it + n_solve  # one application per iteration + the x update at the end of a cycle
-        add("K product: lat_kstencil_kernel" if mf else "K product: kmv_kernel", pc["ms_kmv"], pc["bytes_kmv"], n_pc * (2 * sweeps + 1))
-        add("Schur row: lat_kernel<LAT_S>" if mf else "Schur row: bcd_kernel", pc["ms_schur_row"], pc["bytes_schur_row"], n_pc * sweeps)
+        ms, by = pc["ms"], pc["bytes"]
+        if mf:
+            add("Chebyshev sweep on the Schur complement: ring_sweep_kernel", ms[1], by[0], n_pc * (sweeps - 1))
+            add("Schur right-hand side + first Chebyshev step: lat_kernel<LAT_S>", ms[2], by[1], n_pc)
+            add("t = M_L^-1 (r2 - K M_L^-1 r1): ring_t_kernel", ms[3], by[2], n_pc)
+            add("back substitution chi, phi: ring_back_kernel", ms[4], by[3], n_pc)
+        else:
+            add("K product: kmv_kernel", ms[1], by[0], n_pc * (2 * sweeps + 1))
+            add("Schur row: bcd_kernel", ms[2], by[1], n_pc * sweeps)
         legs["preconditioner application (all its kernels)"] = {"ms": pc["ms_apply"], "launches_per_step": n_pc,
                                                                 "share_of_step": pc["ms_apply"] * n_pc / ms_per_step}
     kry = solver.time_krylov(dim=14, reps=10)

@@ -160,7 +160,8 @@ int pfc_comm_mode(const pfc_handle *h);
 int pfc_time_comm(pfc_handle *h, int32_t reps, double *ms3);
 
 /* ---- state (mpi.cpp:278-296 writes Psi_n, Psi_n_1; output reads them mpi.cpp:597-619) ---- */
-int pfc_set_state(pfc_handle *h, const double *Psi_n, const double *Psi_n_1); /* [n_dofs] each */
+int pfc_set_state(pfc_handle *h, const double *Psi_n, const double *Psi_n_1); /* [n_dofs] each; [collective] on the
+                                                                               * lattice path with n_ranks > 1 (ring values) */
 int pfc_get_state(pfc_handle *h, double *Psi_n, double *Psi_n_1);             /* either may be NULL */
 /* The same with what a rank of the MPI original holds (owned_partitioning, mpi.cpp:167-176): arrays [3][n_owned],
  * block b = the contiguous owned dofs block_start[b] + [node_offsets[rank], node_offsets[rank + 1]).
@@ -192,15 +193,23 @@ int pfc_get_dof_permutation(pfc_handle *h, int32_t *internal_of_node);  /* [N] i
  * algorithmic bytes of one launch for the active layout */
 int pfc_time_operator(pfc_handle *h, int32_t reps, double *ms_mean, double *bytes_per_launch);
 int pfc_time_assembly(pfc_handle *h, int32_t reps, double *ms_mean, double *bytes_per_launch);
-/* block-Schur preconditioner legs on resident data: ms[0] one full application P^-1 v, ms[1] one K product
- * (kmv), ms[2] one Schur-row product (Chebyshev step); bytes[] = algorithmic bytes of ms[1], ms[2] launches */
-int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms3, double *bytes2);
+/* block-Schur preconditioner legs on resident data, device time per launch replayed from a CUDA graph:
+ *   ms5[0] one full application P^-1 v (lattice path: including its one halo exchange)
+ *   assembled path: ms5[1] one K product (kmv_kernel), ms5[2] one Schur-row product (bcd_kernel, Chebyshev step)
+ *   lattice path:   ms5[1] one Chebyshev sweep (ring_sweep_kernel), ms5[2] Schur right-hand side + first step
+ *                   (lat_kernel<LAT_S>), ms5[3] t kernel (ring_t_kernel), ms5[4] back substitution (ring_back_kernel)
+ * bytes4[k] = algorithmic bytes of one launch of leg k + 1 (0 where the leg does not exist) */
+int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms5, double *bytes4);
 /* consistency of redundant kernel forms on a deterministic pseudo-random field (lattice path: K product as node
  * stencil vs cell quadrature); max_rel = max |a - b| / max |a|.  0 when the handle has no redundant form. [collective] */
 int pfc_selfcheck(pfc_handle *h, double *max_rel);
-/* EXPERIMENTAL (not yet run on a GPU): the one-kernel constant-coefficient Chebyshev sweep that
- * PFC_SMOOTHER=1 selects on a single rank, compared with the composition of the K-stencil and mass-stencil kernels */
+/* lattice path with the preconditioner: S~ x by the one-kernel streaming Chebyshev sweep (csrc/pfc_ring.cuh) against the
+ * composition of the K-stencil and mass-stencil kernels with a halo exchange before every product [collective] */
 int pfc_selfcheck_smoother(pfc_handle *h, double *max_rel);
+/* which operator path pfc_setup chose: returns PFC_OPERATOR_ASSEMBLED, PFC_OPERATOR_MATRIX_FREE (lattice kernels) or
+ * PFC_OPERATOR_MATRIX_FREE_GENERAL, -1 before pfc_setup; note (optional) receives why the lattice kernels were declined
+ * when PFC_OPERATOR_MATRIX_FREE was asked for and the general kernel is in charge (empty otherwise) */
+int pfc_operator_info(const pfc_handle *h, char *note, int32_t note_len);
 
 /* ---- stress projection ------------------------------------------------------
  * Replaces StressCalculatorMPI<dim>::calculate_stress(mpi_communicator, Psi_dof_handler, Psi, eps)
@@ -306,6 +315,21 @@ typedef struct pfc_lattice_view
   char why[128];
 } pfc_lattice_view;
 void pfc_plan_get_lattice(const pfc_plan *p, pfc_lattice_view *view);
+/* Deep ghost ring of the lattice path (what pfc_setup builds after the ranks exchanged their places on the lattice;
+ * csrc/pfc_ring_plan.cpp).  plans[r] = the plan of rank r built with flags 3; afterwards rank r's local positions are
+ * the padded rectangle [0, fw) x [0, fh) with the owned free nodes at [ex0, ex0 + w) x [ey0, ey0 + h); a position
+ * outside has the ghost id Np + ring index and is filled by the halo exchange described by the lists:
+ *   tail[self_dst[i]] = owned[self_src[i]]                  positions this rank owns itself (periodic wrap-around)
+ *   peer k sends owned[send_rows[send_ptr[k] ..)]; the j-th value received (peer-major) goes to ring position recv_pos[j] */
+typedef struct pfc_ring_view
+{
+  int32_t active, depth, ex0, ey0, fw, fh, ncx, ncy;
+  int64_t n_ring, n_self, n_recv, n_send, n_peers;
+  const int32_t *self_src, *self_dst, *recv_pos, *send_rows, *peers;
+  const int64_t *recv_ptr, *send_ptr;
+} pfc_ring_view;
+int  pfc_plan_ring_overlay(pfc_plan *const *plans, int32_t n_ranks, int32_t depth, char *err, int32_t err_len);
+void pfc_plan_get_ring(const pfc_plan *p, pfc_ring_view *view);
 void pfc_plan_get_view(const pfc_plan *p, pfc_plan_view *view);
 /* monolithic CSR the reference would build (mpi.cpp:220-244) + where each entry lives:
  * block_of 0 B, 1 C, 2 D, 3 K, 4 M; pos_of = entry position in the SELL arrays (single rank) */

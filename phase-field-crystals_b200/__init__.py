@@ -99,6 +99,13 @@ class LatticeView(C.Structure):
                [("hx", C.c_double), ("hy", C.c_double), ("lut", _i32p), ("why", C.c_char * 128)]
 
 
+class RingView(C.Structure):
+    _fields_ = [(k, C.c_int32) for k in ("active", "depth", "ex0", "ey0", "fw", "fh", "ncx", "ncy")] + \
+               [(k, C.c_int64) for k in ("n_ring", "n_self", "n_recv", "n_send", "n_peers")] + \
+               [(k, _i32p) for k in ("self_src", "self_dst", "recv_pos", "send_rows", "peers")] + \
+               [("recv_ptr", _i64p), ("send_ptr", _i64p)]
+
+
 # every symbol include/pfc_b200.h declares (tests check the library exports all of them)
 EXPORTED_SYMBOLS = [
     "pfc_default_params", "pfc_create", "pfc_destroy", "pfc_last_error", "pfc_version", "pfc_setup",
@@ -108,7 +115,7 @@ EXPORTED_SYMBOLS = [
     "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_selfcheck_smoother", "pfc_stress", "pfc_stress_owned", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
     "pfc_standin_create_ex", "pfc_standin_destroy",
     "pfc_standin_mesh", "pfc_standin_n_nodes", "pfc_standin_support_points",
-    "pfc_standin_hexagonal_lattice", "pfc_standin_polycrystal", "pfc_plan_build", "pfc_plan_build_ex", "pfc_plan_get_lattice", "pfc_plan_get_view", "pfc_plan_monolithic",
+    "pfc_standin_hexagonal_lattice", "pfc_standin_polycrystal", "pfc_plan_build", "pfc_plan_build_ex", "pfc_plan_get_lattice", "pfc_plan_ring_overlay", "pfc_plan_get_ring", "pfc_operator_info", "pfc_plan_get_view", "pfc_plan_monolithic",
     "pfc_plan_destroy",
 ]
 
@@ -207,6 +214,10 @@ def lib():
     L.pfc_plan_build_ex.argtypes = [C.POINTER(MeshStruct), C.c_int32, C.c_int32, C.POINTER(hp), C.c_char_p, C.c_int32]
     L.pfc_plan_get_lattice.argtypes = [hp, C.POINTER(LatticeView)]
     L.pfc_plan_get_lattice.restype = None
+    L.pfc_plan_ring_overlay.argtypes = [C.POINTER(hp), C.c_int32, C.c_int32, C.c_char_p, C.c_int32]
+    L.pfc_plan_get_ring.argtypes = [hp, C.POINTER(RingView)]
+    L.pfc_plan_get_ring.restype = None
+    L.pfc_operator_info.argtypes = [hp, C.c_char_p, C.c_int32]
     L.pfc_plan_get_view.argtypes = [hp, C.POINTER(PlanView)]
     L.pfc_plan_get_view.restype = None
     L.pfc_plan_monolithic.argtypes = [hp, _i64p, _i32p, C.POINTER(C.c_int8), _i32p]
@@ -362,6 +373,26 @@ class HostPlan:
         self.peers = get(v.peers, (self.n_peers,))
         self.recv_ptr = arr(v.recv_ptr, (self.n_peers + 1,)) if self.n_peers else np.zeros(1, np.int64)
 
+    def ring(self):
+        """view of the ring overlay (after ring_overlay([...plans...], depth))"""
+        v = RingView()
+        lib().pfc_plan_get_ring(self._h, C.byref(v))
+        out = {k: getattr(v, k) for k, _ in RingView._fields_[:13]}
+        arr = np.ctypeslib.as_array
+
+        def get(ptr, n, dt=np.int32):
+            return arr(ptr, (n,)).copy() if n > 0 and bool(ptr) else np.zeros(0, dt)
+
+        out.update(self_src=get(v.self_src, v.n_self), self_dst=get(v.self_dst, v.n_self), recv_pos=get(v.recv_pos, v.n_recv),
+                   send_rows=get(v.send_rows, v.n_send), peers=get(v.peers, v.n_peers),
+                   recv_ptr=get(v.recv_ptr, v.n_peers + 1, np.int64), send_ptr=get(v.send_ptr, v.n_peers + 1, np.int64))
+        pv = PlanView()
+        lib().pfc_plan_get_view(self._h, C.byref(pv))
+        out["n_ghost"] = pv.n_ghost
+        out["ghost_global"] = get(pv.ghost_global, pv.n_ghost)
+        out["slave_id"], out["slave_master"] = get(pv.slave_id, pv.n_slaves), get(pv.slave_master, pv.n_slaves)
+        return out
+
     def monolithic(self):
         n = 3 * self.N_global
         rp = np.empty(n + 1, np.int64)
@@ -384,6 +415,15 @@ class HostPlan:
             self.close()
         except Exception:
             pass
+
+
+def ring_overlay(plans, depth):
+    """pfc_plan_ring_overlay over the HostPlans of all ranks of a partition (flags 3), in rank order"""
+    arr = (C.c_void_p * len(plans))(*[p._h for p in plans])
+    err = C.create_string_buffer(512)
+    rc = lib().pfc_plan_ring_overlay(arr, len(plans), depth, err, 512)
+    if rc != PFC_OK:
+        raise PfcError(rc, err.value.decode())
 
 
 class Solver:
@@ -534,9 +574,15 @@ class Solver:
         return v.value
 
     def time_precond(self, reps=10):
-        ms, by = (C.c_double * 3)(), (C.c_double * 2)()
+        """legs of include/pfc_b200.h pfc_time_precond: ms[0..4], bytes[0..3] (bytes[k] belongs to ms[k + 1])"""
+        ms, by = (C.c_double * 5)(), (C.c_double * 4)()
         self._check(lib().pfc_time_precond(self._h, reps, ms, by))
-        return {"ms_apply": ms[0], "ms_kmv": ms[1], "ms_schur_row": ms[2], "bytes_kmv": by[0], "bytes_schur_row": by[1]}
+        return {"ms": list(ms), "bytes": list(by), "ms_apply": ms[0]}
+
+    def operator_info(self):
+        buf = C.create_string_buffer(512)
+        kind = lib().pfc_operator_info(self._h, buf, 512)
+        return kind, buf.value.decode()
 
     def time_assembly(self, reps=5):
         ms, by = C.c_double(), C.c_double()

@@ -1,7 +1,9 @@
 // pfc_api.cu — C ABI (include/pfc_b200.h) over the CUDA kernels: lifecycle, setup, state.
 // The solver drivers live in pfc_solver.cu.
 #include <cmath>
+#include <cstdio>
 #include <cstring>
+#include <string>
 
 #include "pfc_comm.h"
 #include "pfc_handle.h"
@@ -162,9 +164,44 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
   Plan &P = h->plan;
   const int plan_flags = h->prm.operator_kind == PFC_OPERATOR_MATRIX_FREE ? (PLAN_LATTICE | PLAN_SKIP_TABLES) : 0;
   int rc = build_plan(*mesh, h->prm.degree, P, plan_flags);
-  h->lat = P.lat.active;
   if (rc != PFC_OK)
     return h->fail(rc, "pfc_setup: %s", P.error.c_str());
+  h->lat = false;
+  h->operator_note.clear();
+  if (plan_flags & PLAN_LATTICE)
+    { // the lattice kernels need every rank on the lattice: the ranks exchange their places on it (collective) and
+      // replace deal.II's one-cell ghost layer by the deep ring; otherwise all ranks take the general cell kernel
+      std::vector<RingCard> cards;
+      rc = comm_gather_cards(h, ring_card(P), cards);
+      if (rc != PFC_OK)
+        return rc;
+      std::string why;
+      for (size_t r = 0; r < cards.size(); ++r)
+        if (!cards[r].active && why.empty())
+          why = "rank " + std::to_string(r) + (r == (size_t)P.rank ? ": " + P.lat.why : std::string(": no uniform lattice with a rectangular owned region"));
+      if (why.empty())
+        {
+          // depth: what one preconditioned GMRES iteration consumes (t, Schur right-hand side, Chebyshev sweeps,
+          // back substitution, operator), DESIGN.md "ring"; unpreconditioned: the operator's one cell
+          const int p = h->prm.degree;
+          const int depth = h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR ? (3 * h->sweeps + 2) * p : p;
+          rc = ring_overlay(P, cards, depth);
+          if (rc != PFC_OK)
+            why = P.error;
+        }
+      if (why.empty())
+        h->lat = true;
+      else
+        {
+          h->operator_note = "lattice kernels declined (" + why + "): using the general colour-ordered matrix-free kernel";
+          if (P.lat.active)
+            { // this rank's plan skipped the tables the general kernel needs
+              rc = build_plan(*mesh, h->prm.degree, P, 0);
+              if (rc != PFC_OK)
+                return h->fail(rc, "pfc_setup: %s", P.error.c_str());
+            }
+        }
+    }
 
   // host pattern check (mpi.cpp:232-244): bit-identical or refused
   if (mesh->row_ptr && mesh->col_idx && P.n_ranks == 1 && P.has_tables)
@@ -176,7 +213,13 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
           std::memcmp(ci.data(), mesh->col_idx, ci.size() * sizeof(int32_t)) != 0)
         return h->fail(PFC_ERR_BAD_ARGUMENT, "pfc_setup: host sparsity pattern differs from the derived pattern");
     }
-  if (P.n_ranks > 1)
+  if (h->lat)
+    {
+      rc = comm_ring_upload(h);
+      if (rc != PFC_OK)
+        return rc;
+    }
+  else if (P.n_ranks > 1)
     {
       rc = comm_exchange_send_lists(h);
       if (rc != PFC_OK)
@@ -210,8 +253,9 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
         for (int c = 0; c < 3; ++c)
           map[P.block_start[c] + P.perm[r]] = c * P.Np + r;
     for (int64_t g = 0; g < P.n_ghost; ++g)
-      for (int c = 0; c < 3; ++c)
-        map[P.block_start[c] + P.ghost_global[g]] = 3 * (P.Np + g) + c;
+      if (P.ghost_global[g] >= 0) // ring overlay: only the positions of the handed-over frame have a global id
+        for (int c = 0; c < 3; ++c)
+          map[P.block_start[c] + P.ghost_global[g]] = 3 * (P.Np + g) + c;
     PFC_CUDA(h, h->d_api_map.upload(map, s));
     PFC_CUDA(h, cudaStreamSynchronize(s));
   }
@@ -279,7 +323,6 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
   h->is_setup = true;
   // iterate-independent blocks M and K, once (they are re-assembled every Newton iteration
   // upstream, mpi.cpp:435-443, with identical values); the lattice path stores no matrix at all
-  h->smoother_const = h->lat && P.n_ranks == 1 && getenv("PFC_SMOOTHER") && atoi(getenv("PFC_SMOOTHER")) == 1;
   rc = h->lat ? lat_setup(h) : launch_assembly(h, true);
   if (rc != PFC_OK)
     {
@@ -316,6 +359,12 @@ extern "C" int pfc_set_state(pfc_handle *h, const double *Psi_n, const double *P
         PFC_CUDA(h, cudaMemcpyAsync(h->d_io.p, src[k], n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
       scatter_kernel<<<blocks, 256, 0, h->stream>>>(dst[k], h->d_io.p, h->d_api_map.p, n);
       h->launches++;
+      if (h->lat)
+        { // the ring beyond the handed-over ghost layer comes from its owners [collective for n_ranks > 1]
+          const int rc = halo_exchange(h, dst[k]);
+          if (rc != PFC_OK)
+            return rc;
+        }
     }
   PFC_CUDA(h, cudaGetLastError());
   PFC_CUDA(h, cudaStreamSynchronize(h->stream));
@@ -337,6 +386,17 @@ static int owned_map(pfc_handle *h)
   PFC_CUDA(h, h->d_owned_map.upload(map, h->stream));
   PFC_CUDA(h, cudaStreamSynchronize(h->stream));
   return PFC_OK;
+}
+
+extern "C" int pfc_operator_info(const pfc_handle *h, char *buf, int32_t buflen)
+{
+  if (!h || !h->is_setup)
+    return -1;
+  const int kind = h->lat ? PFC_OPERATOR_MATRIX_FREE
+                          : (h->prm.operator_kind == PFC_OPERATOR_ASSEMBLED ? PFC_OPERATOR_ASSEMBLED : PFC_OPERATOR_MATRIX_FREE_GENERAL);
+  if (buf && buflen > 0)
+    std::snprintf(buf, (size_t)buflen, "%s", h->operator_note.c_str());
+  return kind;
 }
 
 extern "C" int64_t pfc_n_owned_nodes(const pfc_handle *h) { return (h && h->is_setup) ? h->plan.n_owned : -1; }
@@ -506,6 +566,7 @@ extern "C" int pfc_get_dof_permutation(pfc_handle *h, int32_t *internal_of_node)
   for (int64_t i = 0; i < P.n_owned; ++i)
     internal_of_node[P.own0 + i] = P.iperm[i];
   for (int64_t g = 0; g < P.n_ghost; ++g)
-    internal_of_node[P.ghost_global[g]] = (int32_t)(P.Np + g);
+    if (P.ghost_global[g] >= 0)
+      internal_of_node[P.ghost_global[g]] = (int32_t)(P.Np + g);
   return PFC_OK;
 }

@@ -266,61 +266,140 @@ int comm_exchange_send_lists(pfc_handle *h)
   return PFC_OK;
 }
 
-int halo_exchange(pfc_handle *h, double *v, const Ctl *ctl)
+// ring overlay (lattice path): tail[self_dst] = owned[self_src] (positions this rank owns itself: periodic wrap) and,
+// on the NCCL transport, received values from the staging buffer to their ring positions
+template <int NC>
+static __global__ void ring_unpack_kernel(double *__restrict__ v, int64_t Np, const int32_t *__restrict__ self_src,
+                                          const int32_t *__restrict__ self_dst, int64_t n_self,
+                                          const double *__restrict__ stage, const int32_t *__restrict__ recv_pos,
+                                          int64_t n_recv, const Ctl *ctl)
+{
+  if (ctl && ctl->state != 0)
+    return;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = tid; i < n_self; i += nth)
+    {
+      const int64_t s = self_src[i], t = Np + self_dst[i];
+      if (NC == 3)
+        {
+#pragma unroll
+          for (int c = 0; c < 3; ++c)
+            v[3 * t + c] = v[(int64_t)c * Np + s];
+        }
+      else
+        v[t] = v[s];
+    }
+  for (int64_t g = tid; g < n_recv; g += nth)
+    {
+      const int64_t t = Np + recv_pos[g];
+      if (NC == 3)
+        {
+#pragma unroll
+          for (int c = 0; c < 3; ++c)
+            v[3 * t + c] = stage[3 * g + c];
+        }
+      else
+        v[t] = stage[g];
+    }
+}
+
+static int ring_unpack(pfc_handle *h, double *v, int nc, bool staged, const Ctl *ctl)
 {
   const Plan &P = h->plan;
-  if (P.n_ranks <= 1)
+  const int64_t n_self = (int64_t)P.ring.self_src.size(), n_recv = staged ? (int64_t)P.ring.recv_pos.size() : 0;
+  const int64_t work = std::max(n_self, n_recv);
+  if (work == 0)
     return PFC_OK;
-  if (h->p2p)
-    return p2p_halo(h, v, 3, ctl);
-  NcclApi &n = nccl();
-  ncclComm_t comm = (ncclComm_t)h->comm;
-  const int64_t ns = (int64_t)P.send_rows.size();
-  if (ns > 0)
-    {
-      halo_pack_kernel<<<(int)((ns + 255) / 256), 256, 0, h->stream>>>(h->d_send_buf.p, v, h->d_send_rows.p, ns, P.Np);
-      h->launches++;
-    }
-  PFC_NCCL(h, n.GroupStart());
-  for (size_t p = 0; p < P.peers.size(); ++p)
-    {
-      const int64_t nr = P.recv_ptr[p + 1] - P.recv_ptr[p], nsd = P.send_ptr[p + 1] - P.send_ptr[p];
-      if (nsd > 0)
-        PFC_NCCL(h, n.Send(h->d_send_buf.p + 3 * P.send_ptr[p], (size_t)(3 * nsd), ncclDouble, P.peers[p], comm, h->stream));
-      if (nr > 0)
-        PFC_NCCL(h, n.Recv(v + 3 * P.Np + 3 * P.recv_ptr[p], (size_t)(3 * nr), ncclDouble, P.peers[p], comm, h->stream));
-    }
-  PFC_NCCL(h, n.GroupEnd());
+  const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((work + 255) / 256, (int64_t)h->n_sm * 4));
+  if (nc == 3)
+    ring_unpack_kernel<3><<<blocks, 256, 0, h->stream>>>(v, P.Np, h->d_self_src.p, h->d_self_dst.p, n_self, h->d_recv_buf.p,
+                                                          h->d_recv_pos.p, n_recv, ctl);
+  else
+    ring_unpack_kernel<1><<<blocks, 256, 0, h->stream>>>(v, P.Np, h->d_self_src.p, h->d_self_dst.p, n_self, h->d_recv_buf.p,
+                                                          h->d_recv_pos.p, n_recv, ctl);
+  h->launches++;
   return PFC_OK;
 }
 
-int halo_exchange_scalar(pfc_handle *h, double *v, const Ctl *ctl)
+static int nccl_halo(pfc_handle *h, double *v, int nc, const Ctl *ctl)
 {
   const Plan &P = h->plan;
-  if (P.n_ranks <= 1)
-    return PFC_OK;
-  if (h->p2p)
-    return p2p_halo(h, v, 1, ctl);
   NcclApi &n = nccl();
   ncclComm_t comm = (ncclComm_t)h->comm;
+  const bool ring = P.ring.active;
   const int64_t ns = (int64_t)P.send_rows.size();
   if (ns > 0)
     {
-      halo_pack1_kernel<<<(int)((ns + 255) / 256), 256, 0, h->stream>>>(h->d_send_buf.p, v, h->d_send_rows.p, ns);
+      if (nc == 3)
+        halo_pack_kernel<<<(int)((ns + 255) / 256), 256, 0, h->stream>>>(h->d_send_buf.p, v, h->d_send_rows.p, ns, P.Np);
+      else
+        halo_pack1_kernel<<<(int)((ns + 255) / 256), 256, 0, h->stream>>>(h->d_send_buf.p, v, h->d_send_rows.p, ns);
       h->launches++;
     }
+  // ghosts sorted by owner: received straight into the tail; ring: into the staging buffer, then to their positions
+  double *dst = ring ? h->d_recv_buf.p : v + (int64_t)nc * P.Np;
   PFC_NCCL(h, n.GroupStart());
   for (size_t p = 0; p < P.peers.size(); ++p)
     {
       const int64_t nr = P.recv_ptr[p + 1] - P.recv_ptr[p], nsd = P.send_ptr[p + 1] - P.send_ptr[p];
       if (nsd > 0)
-        PFC_NCCL(h, n.Send(h->d_send_buf.p + P.send_ptr[p], (size_t)nsd, ncclDouble, P.peers[p], comm, h->stream));
+        PFC_NCCL(h, n.Send(h->d_send_buf.p + nc * P.send_ptr[p], (size_t)(nc * nsd), ncclDouble, P.peers[p], comm, h->stream));
       if (nr > 0)
-        PFC_NCCL(h, n.Recv(v + P.Np + P.recv_ptr[p], (size_t)nr, ncclDouble, P.peers[p], comm, h->stream));
+        PFC_NCCL(h, n.Recv(dst + nc * P.recv_ptr[p], (size_t)(nc * nr), ncclDouble, P.peers[p], comm, h->stream));
     }
   PFC_NCCL(h, n.GroupEnd());
+  if (ring)
+    return ring_unpack(h, v, nc, true, ctl);
   return PFC_OK;
 }
+
+static int halo_any(pfc_handle *h, double *v, int nc, const Ctl *ctl)
+{
+  const Plan &P = h->plan;
+  if (P.n_ranks <= 1)
+    return P.ring.active ? ring_unpack(h, v, nc, false, ctl) : PFC_OK; // single rank: periodic wrap-around copies
+  if (h->p2p)
+    return p2p_halo(h, v, nc, ctl);
+  return nccl_halo(h, v, nc, ctl);
+}
+
+// device copies of the ring lists (after ring_overlay); the NCCL transport also gets its staging buffers
+int comm_ring_upload(pfc_handle *h)
+{
+  const Plan &P = h->plan;
+  cudaStream_t s = h->stream;
+  PFC_CUDA(h, h->d_self_src.upload(P.ring.self_src, s));
+  PFC_CUDA(h, h->d_self_dst.upload(P.ring.self_dst, s));
+  PFC_CUDA(h, h->d_recv_pos.upload(P.ring.recv_pos, s));
+  PFC_CUDA(h, h->d_send_rows.upload(P.send_rows, s));
+  PFC_CUDA(h, h->d_send_buf.alloc(3 * std::max<size_t>(P.send_rows.size(), 1)));
+  PFC_CUDA(h, h->d_recv_buf.alloc(3 * std::max<size_t>(P.ring.recv_pos.size(), 1)));
+  PFC_CUDA(h, cudaStreamSynchronize(s));
+  return PFC_OK;
+}
+
+// all ranks' RingCards (collective); single rank: the own card
+int comm_gather_cards(pfc_handle *h, const RingCard &mine, std::vector<RingCard> &all)
+{
+  const int R = h->plan.n_ranks;
+  all.assign((size_t)R, mine);
+  if (R <= 1)
+    return PFC_OK;
+  static_assert(sizeof(RingCard) % 8 == 0, "RingCard is exchanged as int64 words");
+  NcclApi &n = nccl();
+  const size_t words = sizeof(RingCard) / 8;
+  DevBuf<long long> d_mine, d_all;
+  PFC_CUDA(h, d_mine.alloc(words));
+  PFC_CUDA(h, d_all.alloc(words * R));
+  PFC_CUDA(h, cudaMemcpyAsync(d_mine.p, &mine, sizeof(RingCard), cudaMemcpyHostToDevice, h->stream));
+  PFC_NCCL(h, n.AllGather(d_mine.p, d_all.p, words, ncclInt64, (ncclComm_t)h->comm, h->stream));
+  PFC_CUDA(h, cudaMemcpyAsync(all.data(), d_all.p, sizeof(RingCard) * R, cudaMemcpyDeviceToHost, h->stream));
+  PFC_CUDA(h, cudaStreamSynchronize(h->stream));
+  return PFC_OK;
+}
+
+int halo_exchange(pfc_handle *h, double *v, const Ctl *ctl) { return halo_any(h, v, 3, ctl); }
+int halo_exchange_scalar(pfc_handle *h, double *v, const Ctl *ctl) { return halo_any(h, v, 1, ctl); }
 
 // =====================================================================================================
 // Peer-to-peer path over NVLink / NVSwitch (single node).  A preconditioned GMRES iteration has ~14 halo
@@ -353,7 +432,11 @@ struct P2PHaloArgs
   int64_t send_ptr[kMaxRanksP2P + 1];
   int n_peers;
   const uint4 *mine;              // own buffer
-  int64_t my_half, n_ghost;
+  int64_t my_half, n_ghost;       // n_ghost: values received (slots of the own buffer in use)
+  // ring overlay: the k-th received value goes to ring position recv_pos[k] (NULL: ghost k), and the positions this
+  // rank owns itself are copied locally
+  const int32_t *recv_pos, *self_src, *self_dst;
+  int64_t n_self;
 };
 
 
@@ -382,17 +465,30 @@ static __global__ void __launch_bounds__(256) p2p_halo_kernel(P2PHaloArgs H, dou
       for (int c = 0; c < NC; ++c)
         ll_store(d + c, v[(int64_t)c * Np + r], tag);
     }
-  const uint4 *m = H.mine + par * H.my_half;
-  for (int64_t g = tid; g < H.n_ghost; g += nth)
+  for (int64_t i = tid; i < H.n_self; i += nth)
     {
+      const int64_t s = H.self_src[i], t = Np + H.self_dst[i];
       if (NC == 3)
         {
 #pragma unroll
           for (int c = 0; c < 3; ++c)
-            v[3 * Np + 3 * g + c] = ll_wait(m + 3 * g + c, tag);
+            v[3 * t + c] = v[(int64_t)c * Np + s];
         }
       else
-        v[Np + g] = ll_wait(m + g, tag);
+        v[t] = v[s];
+    }
+  const uint4 *m = H.mine + par * H.my_half;
+  for (int64_t g = tid; g < H.n_ghost; g += nth)
+    {
+      const int64_t t = Np + (H.recv_pos ? (int64_t)H.recv_pos[g] : g);
+      if (NC == 3)
+        {
+#pragma unroll
+          for (int c = 0; c < 3; ++c)
+            v[3 * t + c] = ll_wait(m + 3 * g + c, tag);
+        }
+      else
+        v[t] = ll_wait(m + g, tag);
     }
   // the last CTA to finish advances the epoch (the next collective kernel starts after this one has ended)
   __syncthreads();
@@ -450,8 +546,15 @@ static int p2p_halo(pfc_handle *h, double *v, int nc, const Ctl *ctl)
   H.send_ptr[H.n_peers] = P.send_ptr[H.n_peers];
   H.mine = S.ll[S.me];
   H.my_half = 3 * P.n_ghost;
-  H.n_ghost = P.n_ghost;
-  const int64_t work = std::max<int64_t>(H.send_ptr[H.n_peers], P.n_ghost);
+  H.n_ghost = P.ring.active ? (int64_t)P.ring.recv_pos.size() : P.n_ghost;
+  if (P.ring.active)
+    {
+      H.recv_pos = h->d_recv_pos.p;
+      H.self_src = h->d_self_src.p;
+      H.self_dst = h->d_self_dst.p;
+      H.n_self = (int64_t)P.ring.self_src.size();
+    }
+  const int64_t work = std::max<int64_t>(std::max<int64_t>(H.send_ptr[H.n_peers], H.n_ghost), H.n_self);
   const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>((work + 255) / 256, (int64_t)h->n_sm * 2));
   if (nc == 3)
     p2p_halo_kernel<3><<<blocks, 256, 0, h->stream>>>(H, v, h->d_send_rows.p, P.Np, S.sync[S.me], ctl);

@@ -5,6 +5,7 @@
 #pragma once
 #include <cstddef>
 #include <cstdint>
+#include <vector>
 
 struct pfc_handle;
 
@@ -15,6 +16,9 @@ struct Ctl;
 // ranks: it derives from all-reduced values); NCCL operations always run
 void comm_destroy(pfc_handle *h);
 int comm_exchange_send_lists(pfc_handle *h);           // after build_plan: fills plan.send_ptr / send_rows
+struct RingCard;
+int comm_gather_cards(pfc_handle *h, const RingCard &mine, std::vector<RingCard> &all); // lattice path: collective
+int comm_ring_upload(pfc_handle *h);                   // after ring_overlay: device copies of the ring lists
 int halo_exchange(pfc_handle *h, double *v, const Ctl *ctl = nullptr);           // v's ghost tail := owners' values (stream-ordered)
 int halo_exchange_scalar(pfc_handle *h, double *v, const Ctl *ctl = nullptr);    // scalar field [owned Np | ghosts]
 int allreduce_sum(pfc_handle *h, double *dev, size_t n, const Ctl *ctl = nullptr); // in place, stream-ordered; no-op on one rank

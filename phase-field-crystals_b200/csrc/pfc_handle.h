@@ -83,7 +83,7 @@ struct pfc_handle
   pfc::DevBuf<double> d_cell_h, d_tab;
   pfc::DevBuf<int64_t> d_slice_ptr, d_api_map, d_stress_map, d_owned_map;
   pfc::DevBuf<double> d_stress, d_stress_io; // pfc_stress work fields (allocated on first use)
-  bool smoother_const = false; // EXPERIMENTAL: PFC_SMOOTHER=1, single rank, lattice path (pfc_lattice_smooth.cuh)
+  std::string operator_note;   // why the lattice kernels were declined (pfc_operator_info)
   bool stress_valid = false;
   bool rhs_valid = false; // d_rhs holds the right-hand side of the last assembly (system_rhs as output_rhs sees it)
   int stress_map_owned = -1; // which output map d_stress_map holds (-1 none, 0 [4][N], 1 [4][n_owned])
@@ -111,8 +111,8 @@ struct pfc_handle
   // multi-GPU
   ncclComm *comm = nullptr;
   int comm_rank = 0, comm_size = 1;
-  pfc::DevBuf<int32_t> d_send_rows;
-  pfc::DevBuf<double> d_send_buf;
+  pfc::DevBuf<int32_t> d_send_rows, d_self_src, d_self_dst, d_recv_pos; // ring overlay lists (pfc_ring_plan.cpp)
+  pfc::DevBuf<double> d_send_buf, d_recv_buf;
   // every vector that takes part in a halo exchange lives in one allocation, so that peers can address it:
   //   [n3 three-component vectors of `stride` doubles: Krylov basis, x, z, u | 12 scalar fields of `sstride`]
   pfc::DevBuf<double> d_arena;
@@ -134,7 +134,6 @@ struct pfc_handle
   // the uniform periodic tensor lattice
   bool lat = false;
   bool lat_k_by_cells = false; // K product by the cell-quadrature kernel instead of the node stencil (self-check)
-  pfc::DevBuf<int32_t> d_lut;
   pfc::LatGeom lat_geom;
 
   int64_t launches = 0;

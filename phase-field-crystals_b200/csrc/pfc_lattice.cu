@@ -5,9 +5,10 @@
 #include <cstring>
 #include <vector>
 
+#include "pfc_comm.h"
 #include "pfc_handle.h"
 #include "pfc_lattice.cuh"
-#include "pfc_lattice_smooth.cuh"
+#include "pfc_ring.cuh"
 
 namespace pfc
 {
@@ -60,6 +61,8 @@ LatOp lat_op(const pfc_handle *h)
   o.theta = h->prm.theta;
   o.eps = h->prm.eps;
   o.inv_ml = h->d_inv_ml.p;
+  o.lo = -1;
+  o.add_c = -1;
   return o;
 }
 
@@ -124,18 +127,51 @@ int lat_launch(pfc_handle *h, int mode, const LatOp &op, const Ctl *ctl)
   return h->fail(PFC_ERR_BAD_ARGUMENT, "lat_launch: unknown mode");
 }
 
-// EXPERIMENTAL (PFC_SMOOTHER=1): one constant-coefficient Chebyshev sweep in one kernel, single rank only
-int lat_smooth(pfc_handle *h, const SmoothOp &op, const Ctl *ctl)
+// ---- streaming stencil kernels of the ring path (pfc_ring.cuh) ----------------------------------------------------
+namespace
 {
-  constexpr int TX = 64, TY = 16;
+constexpr int kRingThreads = 128;
+
+// rows per strip: enough CTAs to fill the SMs several times over, strips not shorter than 16 rows (every strip
+// re-reads its 2 HY warm-up rows)
+int ring_rows_per_strip(const pfc_handle *h, int col_blocks, int rows)
+{
+  const int want = 8 * h->n_sm;
+  const int strips = std::max(1, want / std::max(1, col_blocks));
+  return std::min(256, std::max(16, (rows + strips - 1) / strips));
+}
+
+template <int STAGES, class K1, class K2>
+int ring_launch(pfc_handle *h, RingOp op, const Ctl *ctl, K1 q1, K2 q2)
+{
   const LatGeom &G = h->lat_geom;
-  const dim3 grid((G.w + TX - 1) / TX, (G.h + TY - 1) / TY);
-  if (h->plan.degree == 1)
-    lat_smooth_kernel<1, TX, TY><<<grid, kSmoothThreads, lat_smooth_smem<1, TX, TY>(), h->stream>>>(G, op, ctl);
+  const int p = h->plan.degree, outw = kRingThreads - 2 * STAGES * p;
+  const int cols = G.fw - 2 * op.lo, rows = G.fh - 2 * op.lo;
+  if (cols <= 0 || rows <= 0 || op.lo < STAGES * p)
+    return h->fail(PFC_ERR_STATE, "ring kernel: window margin %d outside the ring", op.lo);
+  const int cb = (cols + outw - 1) / outw;
+  op.rs = ring_rows_per_strip(h, cb, rows);
+  const dim3 grid(cb, (rows + op.rs - 1) / op.rs);
+  if (p == 1)
+    q1<<<grid, kRingThreads, 0, h->stream>>>(G, op, ctl);
   else
-    lat_smooth_kernel<2, TX, TY><<<grid, kSmoothThreads, lat_smooth_smem<2, TX, TY>(), h->stream>>>(G, op, ctl);
+    q2<<<grid, kRingThreads, 0, h->stream>>>(G, op, ctl);
   h->launches++;
   return PFC_OK;
+}
+} // namespace
+
+int ring_launch_t(pfc_handle *h, const RingOp &op, const Ctl *ctl)
+{
+  return ring_launch<1>(h, op, ctl, ring_t_kernel<1, kRingThreads>, ring_t_kernel<2, kRingThreads>);
+}
+int ring_launch_sweep(pfc_handle *h, const RingOp &op, const Ctl *ctl)
+{
+  return ring_launch<3>(h, op, ctl, ring_sweep_kernel<1, kRingThreads>, ring_sweep_kernel<2, kRingThreads>);
+}
+int ring_launch_back(pfc_handle *h, const RingOp &op, const Ctl *ctl)
+{
+  return ring_launch<2>(h, op, ctl, ring_back_kernel<1, kRingThreads>, ring_back_kernel<2, kRingThreads>);
 }
 
 // nodes N = w h; every field is read once (the halo ring through L2) and every output written once
@@ -149,6 +185,10 @@ double lat_bytes(const pfc_handle *h, int mode)
     case LAT_K: return 32.0 * N;  // v 8 + add 8 + inv_ml 8 + out 8
     case LAT_T: return 48.0 * N;  // psi, chi 16 + four right-hand sides 32
     case LAT_M: return 64.0 * N;  // four fields in, four out
+    case RING_T: return 32.0 * N;     // r1, r2 in, t, m1 out
+    case RING_SWEEP: return 48.0 * N; // x, rhs, dinv, d in, d, x out
+    case RING_BACK: return 40.0 * N;  // psi, r1, r2 in, chi, phi out
+    case RING_RHS: return 72.0 * N;   // m1, t, psi, chi, r0, dinv in, rhs, d, x out
     default: return (h->prm.theta == 1.0 ? 32.0 : 48.0) * N + 32.0 * N; // state in, rhs + 1/diag(B) out
     }
 }
@@ -172,15 +212,17 @@ extern "C" int pfc_selfcheck(pfc_handle *h, double *max_rel)
     return h->fail(PFC_ERR_STATE, "pfc_selfcheck: work space too small");
   double *x = h->d_V.p, *ya = h->d_V.p + h->stride, *yb = h->d_V.p + 2 * h->stride;
   std::vector<double> hx((size_t)n, 0.0), a((size_t)P.Np), b((size_t)P.Np);
-  for (int64_t r = 0; r < n; ++r)
-    { // value tied to the global node so that ghosts agree with their owners without an exchange
-      const int64_t g = r < P.Np ? P.perm[r] : P.ghost_global[r - P.Np];
-      if (g >= 0)
-        hx[r] = 0.5 + (double)(((uint64_t)g * 0x9E3779B97F4A7C15ull >> 40) & 0xFFFF) / 65536.0;
-    }
+  for (int64_t r = 0; r < P.Np; ++r)
+    if (P.perm[r] >= 0)
+      hx[r] = 0.5 + (double)(((uint64_t)P.perm[r] * 0x9E3779B97F4A7C15ull >> 40) & 0xFFFF) / 65536.0;
   cudaStream_t s = h->stream;
   PFC_CUDA(h, cudaMemcpyAsync(x, hx.data(), n * sizeof(double), cudaMemcpyHostToDevice, s));
   PFC_CUDA(h, cudaMemsetAsync(ya, 0, 2 * h->stride * sizeof(double), s));
+  {
+    const int rc = halo_exchange_scalar(h, x); // ring values from their owners
+    if (rc != PFC_OK)
+      return rc;
+  }
   LatOp op = lat_op(h);
   op.s0 = x;
   op.k = 1.0;
@@ -215,18 +257,17 @@ namespace pfc
 int lat_setup(pfc_handle *h)
 {
   const Lattice &L = h->plan.lat;
+  const Ring &R = h->plan.ring; // padded rectangle of the ring overlay: every position has an arithmetic id
   cudaStream_t s = h->stream;
-  PFC_CUDA(h, h->d_lut.upload(L.lut, s));
   LatGeom &G = h->lat_geom;
-  G.ncx = L.ncx;
-  G.ncy = L.ncy;
-  G.ex0 = L.ex0;
-  G.ey0 = L.ey0;
+  G.ncx = R.ncx;
+  G.ncy = R.ncy;
+  G.ex0 = R.ex0;
+  G.ey0 = R.ey0;
   G.w = L.w;
   G.h = L.h;
-  G.fw = L.fw;
-  G.fh = L.fh;
-  G.lut = h->d_lut.p;
+  G.fw = R.fw;
+  G.fh = R.fh;
   G.Np = h->plan.Np;
   G.hx = L.hx;
   G.hy = L.hy;
@@ -234,8 +275,9 @@ int lat_setup(pfc_handle *h)
   G.ihy = 1.0 / L.hy;
   if (h->d_inv_ml.n != (size_t)h->plan.Np)
     PFC_CUDA(h, h->d_inv_ml.alloc(h->plan.Np));
-  if (h->d_dinvB.n != (size_t)h->plan.Np)
-    PFC_CUDA(h, h->d_dinvB.alloc(h->plan.Np));
+  // 1 / diag(B) lives on the ring too (the Chebyshev sweeps run there): [owned | ghosts]
+  PFC_CUDA(h, h->d_dinvB.alloc((size_t)(h->plan.Np + h->plan.n_ghost)));
+  PFC_CUDA(h, cudaMemsetAsync(h->d_dinvB.p, 0, h->d_dinvB.n * sizeof(double), s));
   const int64_t n = h->plan.Np;
   if (h->plan.degree == 1)
     lat_inv_ml_kernel<1><<<(int)((n + 255) / 256), 256, 0, s>>>(G, h->d_inv_ml.p, n);
@@ -249,45 +291,50 @@ int lat_setup(pfc_handle *h)
 }
 } // namespace pfc
 
-// S~ x by lat_smooth_kernel against the composition of the K-stencil and mass-stencil kernels (first thing to run on a GPU
-// when the experimental smoother is taken up: DESIGN.md §9 item 2).  Single rank.
+// S~ x by the streaming sweep kernel (pfc_ring.cuh) against the composition of the K-stencil and mass-stencil kernels with
+// a halo exchange before every product: max |a - b| / max |b| over the owned free nodes.  [collective]
 extern "C" int pfc_selfcheck_smoother(pfc_handle *h, double *max_rel)
 {
   using namespace pfc;
   if (!h || !max_rel)
     return PFC_ERR_BAD_ARGUMENT;
-  if (!h->is_setup || !h->lat || h->plan.n_ranks != 1)
-    return h->fail(PFC_ERR_UNSUPPORTED, "pfc_selfcheck_smoother needs the lattice path on a single rank");
+  if (!h->is_setup || !h->lat)
+    return h->fail(PFC_ERR_UNSUPPORTED, "pfc_selfcheck_smoother needs the lattice path");
   PFC_CUDA(h, cudaSetDevice(h->device));
   const LatGeom &G = h->lat_geom;
-  const int64_t n = (int64_t)G.w * G.h, ss = (h->plan.Np + h->plan.n_ghost + 15) / 16 * 16;
-  const double bbar = 0.9, cbar = -0.3, dtth = h->prm.dt * h->prm.theta;
-  DevBuf<double> F, Gm, Kt2, aux;
-  PFC_CUDA(h, F.alloc((size_t)4 * ss));   // x, t1, t2, (unused)
+  const Plan &P = h->plan;
+  const int p = P.degree;
+  if (h->plan.ring.D < 3 * p)
+    return h->fail(PFC_ERR_UNSUPPORTED, "pfc_selfcheck_smoother needs a ring of depth >= 3 degree (preconditioner on)");
+  const int64_t n = (int64_t)G.w * G.h, ss = (P.Np + P.n_ghost + 15) / 16 * 16;
+  const double bbar = 0.9, dtth = h->prm.dt * h->prm.theta;
+  DevBuf<double> F, Gm, Kt2, out;
+  PFC_CUDA(h, F.alloc((size_t)3 * ss));   // x, t1, t2
   PFC_CUDA(h, Gm.alloc((size_t)4 * ss));  // M x, M t1, M t2
   PFC_CUDA(h, Kt2.alloc((size_t)ss));
-  PFC_CUDA(h, aux.alloc((size_t)4 * ss + 2)); // rhs = 0 | dinv = 1 | d = 0 | xout | cheb
-  std::vector<double> x((size_t)ss, 0.0), ones((size_t)ss, 1.0);
-  uint64_t st = 88172645463325252ull;
+  PFC_CUDA(h, out.alloc((size_t)ss));
+  std::vector<double> x((size_t)ss, 0.0);
   for (int64_t r = 0; r < n; ++r)
-    {
+    { // tied to the global node: the same field on every partition
+      uint64_t st = (uint64_t)P.perm[r] * 0x9E3779B97F4A7C15ull + 88172645463325252ull;
       st ^= st << 13, st ^= st >> 7, st ^= st << 17;
       x[r] = (double)(st >> 11) / 9007199254740992.0 - 0.5;
     }
   cudaStream_t s = h->stream;
   PFC_CUDA(h, cudaMemsetAsync(F.p, 0, F.n * sizeof(double), s));
   PFC_CUDA(h, cudaMemsetAsync(Gm.p, 0, Gm.n * sizeof(double), s));
-  PFC_CUDA(h, cudaMemsetAsync(aux.p, 0, aux.n * sizeof(double), s));
+  PFC_CUDA(h, cudaMemsetAsync(Kt2.p, 0, Kt2.n * sizeof(double), s));
+  PFC_CUDA(h, cudaMemsetAsync(out.p, 0, out.n * sizeof(double), s));
   PFC_CUDA(h, cudaMemcpyAsync(F.p, x.data(), ss * sizeof(double), cudaMemcpyHostToDevice, s));
-  PFC_CUDA(h, cudaMemcpyAsync(aux.p + ss, ones.data(), ss * sizeof(double), cudaMemcpyHostToDevice, s));
-  const double cheb[2] = {0.0, 1.0};
-  PFC_CUDA(h, cudaMemcpyAsync(aux.p + 4 * ss, cheb, sizeof(cheb), cudaMemcpyHostToDevice, s));
-  auto kprod = [&](const double *in, double *out) { // out = (K in) M_L^-1
-    LatOp o = lat_op(h);
-    o.s0 = in;
-    o.k = 1.0;
-    o.out = out;
-    return lat_launch(h, LAT_K, o, nullptr);
+  auto kprod = [&](double *in, double *o) { // o = (K in) M_L^-1
+    int rc = halo_exchange_scalar(h, in);
+    if (rc != PFC_OK)
+      return rc;
+    LatOp q = lat_op(h);
+    q.s0 = in;
+    q.k = 1.0;
+    q.out = o;
+    return lat_launch(h, LAT_K, q, nullptr);
   };
   int rc = kprod(F.p, F.p + ss);
   if (rc == PFC_OK)
@@ -297,35 +344,40 @@ extern "C" int pfc_selfcheck_smoother(pfc_handle *h, double *max_rel)
   if (rc != PFC_OK)
     return rc;
   {
-    LatOp o = lat_op(h);
-    o.s0 = F.p;
-    o.out = Gm.p;
-    o.zstride = ss;
-    o.zmask = 7;
-    rc = lat_launch(h, LAT_M, o, nullptr);
+    LatOp q = lat_op(h);
+    q.s0 = F.p;
+    q.out = Gm.p;
+    q.zstride = ss;
+    q.zmask = 7;
+    rc = lat_launch(h, LAT_M, q, nullptr);
     if (rc != PFC_OK)
       return rc;
   }
-  SmoothOp so{F.p, aux.p, aux.p + ss, aux.p + 4 * ss, aux.p + 2 * ss, aux.p + 3 * ss, bbar, cbar, dtth};
-  rc = lat_smooth(h, so, nullptr);
+  RingOp so;
+  std::memset(&so, 0, sizeof(so));
+  so.x = F.p;
+  so.out = out.p;
+  so.bbar = bbar;
+  so.dtth = dtth;
+  so.lo = 3 * p;
+  so.epi = 3;
+  rc = ring_launch_sweep(h, so, nullptr);
   if (rc != PFC_OK)
     return rc;
   std::vector<double> gm((size_t)3 * ss), kt2((size_t)ss), iml((size_t)n), xo((size_t)ss);
   PFC_CUDA(h, cudaMemcpyAsync(gm.data(), Gm.p, gm.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
   PFC_CUDA(h, cudaMemcpyAsync(kt2.data(), Kt2.p, kt2.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
   PFC_CUDA(h, cudaMemcpyAsync(iml.data(), h->d_inv_ml.p, iml.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
-  PFC_CUDA(h, cudaMemcpyAsync(xo.data(), aux.p + 3 * ss, xo.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+  PFC_CUDA(h, cudaMemcpyAsync(xo.data(), out.p, xo.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
   PFC_CUDA(h, cudaStreamSynchronize(s));
   PFC_CUDA(h, cudaGetLastError());
   double worst = 0, scale = 0;
   for (int64_t r = 0; r < n; ++r)
     {
-      const double ref = bbar * gm[r] - cbar * gm[ss + r] + dtth * (kt2[r] / iml[r] - 2.0 * gm[2 * ss + r]);
-      const double got = x[r] - xo[r]; // d = -(S~ x), xout = x + d
-      worst = std::max(worst, std::fabs(got - ref));
+      const double ref = bbar * gm[r] + dtth * (kt2[r] / iml[r] - 2.0 * gm[2 * ss + r]);
+      worst = std::max(worst, std::fabs(xo[r] - ref));
       scale = std::max(scale, std::fabs(ref));
     }
   *max_rel = scale > 0 ? worst / scale : worst;
   return PFC_OK;
 }
-

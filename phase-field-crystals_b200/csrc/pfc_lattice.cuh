@@ -163,12 +163,28 @@ __device__ __forceinline__ void lat_test(const double (&A)[P + 1][P + 1], const 
   });
 }
 
+// internal id of padded position (ex, ey): owned free node, or ghost Np + ring index (ring_index, pfc_plan.h)
 __device__ __forceinline__ int32_t lat_id(const LatGeom &L, int ex, int ey)
 {
   const int lx = ex - L.ex0, ly = ey - L.ey0;
   if ((unsigned)lx < (unsigned)L.w && (unsigned)ly < (unsigned)L.h)
     return ly * L.w + lx;
-  return __ldg(L.lut + (int64_t)ey * L.fw + ex);
+  int r;
+  if (ey < L.ey0)
+    r = ey * L.fw + ex;
+  else if (ey >= L.ey0 + L.h)
+    r = (ey - L.h) * L.fw + ex;
+  else
+    r = (L.fh - L.h) * L.fw + ly * (L.fw - L.w) + (ex < L.ex0 ? ex : ex - L.w);
+  return (int32_t)L.Np + r;
+}
+
+// output window of a cell kernel: the owned free nodes (lo < 0), or all padded positions at least lo nodes inside
+__device__ __forceinline__ bool lat_in_window(const LatGeom &L, int lo, int X, int Y)
+{
+  if (lo < 0)
+    return (unsigned)(X - L.ex0) < (unsigned)L.w && (unsigned)(Y - L.ey0) < (unsigned)L.h;
+  return X >= lo && X < L.fw - lo && Y >= lo && Y < L.fh - lo;
 }
 
 template <int MODE>
@@ -598,13 +614,13 @@ static __global__ void __launch_bounds__(CX *CY) lat_kernel(LatGeom L, LatOp O, 
       for (int it = 0; it < EIT; ++it)
         {
           const int idx = tid + it * NT;
-          const int lx = nx0 + P + idx % ONX - L.ex0, ly = ny0 + P + idx / ONX - L.ey0;
+          const int X = nx0 + P + idx % ONX, Y = ny0 + P + idx / ONX;
           e_add[it] = e_d[it] = e_dinv[it] = e_s0[it] = 0.0;
-          if (idx < ONX * ONY && (unsigned)lx < (unsigned)L.w && (unsigned)ly < (unsigned)L.h)
+          if (idx < ONX * ONY && lat_in_window(L, O.lo, X, Y))
             {
-              const int64_t r = (int64_t)ly * L.w + lx;
+              const int64_t r = lat_id(L, X, Y);
               if (O.epi != 2)
-                e_add[it] = O.add[r];
+                e_add[it] = O.add[O.add_c < 0 ? r : vaddr(r, O.add_c, Np)];
               if (O.epi == 1)
                 {
                   e_d[it] = O.d[r];
@@ -623,9 +639,8 @@ static __global__ void __launch_bounds__(CX *CY) lat_kernel(LatGeom L, LatOp O, 
       if (idx >= ONX * ONY)
         break;
       const int i = P + idx % ONX, j = P + idx / ONX; // tile node
-      const int lx = nx0 + i - L.ex0, ly = ny0 + j - L.ey0;
-      if ((unsigned)lx >= (unsigned)L.w || (unsigned)ly >= (unsigned)L.h)
-        continue; // not an owned free node
+      if (!lat_in_window(L, MODE == LAT_S ? O.lo : -1, nx0 + i, ny0 + j))
+        continue; // not an owned free node (Schur row: not in the output window)
       const int ccx = i / P, jx = i % P, ccy = j / P, jy = j % P;
       double val[NOUT];
 #pragma unroll
@@ -644,7 +659,7 @@ static __global__ void __launch_bounds__(CX *CY) lat_kernel(LatGeom L, LatOp O, 
           s += s_out[(o * n * n + jy * n + jx) * NT + ccy * CX + ccx];
           val[o] = s;
         }
-      const int64_t r = (int64_t)ly * L.w + lx;
+      const int64_t r = lat_id(L, nx0 + i, ny0 + j); // owned: ly w + lx
       if constexpr (MODE == LAT_J)
         {
           O.out3[r] = val[0];

@@ -9,10 +9,12 @@ namespace pfc
 {
 struct Ctl;
 // ---- kernel arguments ---------------------------------------------------------------------------------
+// Padded rectangle of the ring overlay (Ring in pfc_plan.h): positions [0, fw) x [0, fh), owned free nodes at
+// [ex0, ex0 + w) x [ey0, ey0 + h) with id ly w + lx, everything else a ghost with id Np + ring index (lat_id below);
+// (0, 0) is a cell corner, ncx x ncy cells.
 struct LatGeom
 {
   int32_t ncx, ncy, ex0, ey0, w, h, fw, fh;
-  const int32_t *lut;
   int64_t Np;
   double hx, hy, ihx, ihy; // cell size and its reciprocals
 };
@@ -25,8 +27,9 @@ enum
   LAT_R = 3, // out3 = -R(Psi_n = in3a, Psi_n-1 = in3b), out = 1 / diag(B)   (assemble_system, mpi.cpp:388-417)
   LAT_T = 4, // out[c zstride + r] = right-hand side of the stress projection, c = a*2 + b, from the state in3a
              // (stress_calculator_mpi.cpp:204-314)
-  LAT_M = 5  // out[c zstride + r] = (M s0[c zstride + .])_r for the fields of zmask: consistent mass matrix as a
+  LAT_M = 5, // out[c zstride + r] = (M s0[c zstride + .])_r for the fields of zmask: consistent mass matrix as a
              // node stencil (stress_calculator_mpi.cpp:141-200)
+  RING_T = 6, RING_SWEEP = 7, RING_BACK = 8, RING_RHS = 9 // legs of the ring path (lat_bytes)
 };
 
 struct LatOp
@@ -38,20 +41,29 @@ struct LatOp
   double a, k, sB, sC, sD;
   double dt, theta, eps;
   int epi;
+  int lo;          // LAT_S: output window = padded positions at least lo nodes inside (< 0: the owned free nodes)
+  int add_c;       // LAT_S: `add` is component add_c of a 3-component vector (< 0: scalar field)
   int64_t zstride; // LAT_T / LAT_M: doubles between the batched scalar fields (tensor components)
   int zmask;       // LAT_M: bit c set = field c is processed
   const int *zmask_dev; // LAT_M: if set, the mask is read from the device (and-ed with zmask)
 };
 
 
-// EXPERIMENTAL constant-coefficient Chebyshev sweep (pfc_lattice_smooth.cuh; PFC_SMOOTHER=1, single rank)
-struct SmoothOp
+// streaming stencil kernels of the ring path (pfc_ring.cuh): t kernel, Chebyshev sweep, back substitution
+struct RingOp
 {
-  const double *x, *rhs, *dinv, *cheb; // cheb[0] = coefficient of d, cheb[1] = coefficient of dinv * residual
-  double *d, *xout;
-  double bbar, cbar, dtth;
+  const double *in;          // 3-component input vector r = (r0, r1, r2) of the preconditioner
+  const double *x;           // sweep: scalar field x (or component 0 of xv when x_vec)
+  const double *rhs, *dinv, *cheb;
+  double *d, *t, *m1;        // Chebyshev direction; t kernel outputs
+  double *out;               // sweep output: scalar field, or 3-component vector when out_vec (component 0)
+  double *z;                 // back substitution: 3-component vector, x in component 0, writes chi, phi
+  double bbar, dtth;
+  int lo, rs, epi, out_vec, x_vec;
 };
-int lat_smooth(pfc_handle *h, const SmoothOp &op, const Ctl *ctl);
+int ring_launch_t(pfc_handle *h, const RingOp &op, const Ctl *ctl);
+int ring_launch_sweep(pfc_handle *h, const RingOp &op, const Ctl *ctl);
+int ring_launch_back(pfc_handle *h, const RingOp &op, const Ctl *ctl);
 
 // host side (pfc_lattice.cu)
 int lat_setup(pfc_handle *h);                                              // after build_plan: lut upload, inv_ml

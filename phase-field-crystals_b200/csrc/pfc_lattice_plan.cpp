@@ -188,6 +188,10 @@ bool detect_lattice(const pfc_mesh &m, Plan &P, const std::vector<int32_t> &cnod
     return no("owned rectangle exceeds the period");
   L.w = (int32_t)w;
   L.h = (int32_t)h;
+  L.ox = X0 + (double)xa * (hx / p);
+  L.oy = Y0 + (double)ya * (hy / p);
+  L.Px = Px;
+  L.Py = Py;
   L.order.assign((size_t)(w * h), -1);
   for (int64_t t = own0; t < own1; ++t)
     if (master[t] == t)
@@ -241,6 +245,18 @@ bool detect_lattice(const pfc_mesh &m, Plan &P, const std::vector<int32_t> &cnod
     for (int64_t lx = 0; lx < w; ++lx)
       if (L.lut_global[(size_t)((L.ey0 + ly) * L.fw + L.ex0 + lx)] != L.order[(size_t)(ly * w + lx)])
         return no("frame and owned rectangle disagree");
+  // owned slaves (periodic images this rank numbers itself): their frame position, in internal-id order (global id)
+  for (int64_t t = own0; t < own1; ++t)
+    if (master[t] != t)
+      {
+        if (nx[t] == INT_MIN)
+          return no("an owned slave has no cell of its own");
+        const int64_t fx = nx[t] - xa + L.ex0, fy = ny[t] - ya + L.ey0;
+        if (fx < 0 || fx >= L.fw || fy < 0 || fy >= L.fh)
+          return no("an owned slave lies outside the frame");
+        L.slave_fx.push_back((int32_t)fx);
+        L.slave_fy.push_back((int32_t)fy);
+      }
   L.active = true;
   return true;
 }

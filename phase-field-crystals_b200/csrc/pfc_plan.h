@@ -33,7 +33,45 @@ struct Lattice
   std::vector<int32_t> lut_global; // [fh][fw] global resolved node (detection product)
   std::vector<int32_t> order;      // [w h] global node of owned free node (ly, lx), lexicographic
   std::string why;                 // why the lattice path is not available
+  // what the ring overlay (pfc_ring_plan.cpp) needs to place this rank on the global periodic lattice
+  double ox = 0, oy = 0;           // physical position of the owned free node (0, 0)
+  int64_t Px = 0, Py = 0;          // period in nodes as far as this rank can see it (0: no periodic pair among its nodes)
+  std::vector<int32_t> slave_fx, slave_fy; // frame position of the owned slaves, in the order of their internal ids
 };
+
+// One rank's place on the global lattice: what the ranks all-gather once in pfc_setup (lattice path).
+struct RingCard
+{
+  double ox, oy, hx, hy;     // physical position of owned free node (0, 0); cell size
+  int64_t Px, Py;            // period in nodes (0 if unknown to the rank)
+  int32_t w, h, ex0, ey0;    // owned rectangle; its position in the rank's one-cell frame (ex0 mod p = node type)
+  int32_t p, active;
+};
+
+// Deep ghost ring of the lattice path (pfc_ring_plan.cpp, DESIGN.md "ring").  The rank's local index space becomes the
+// padded rectangle [0, fw) x [0, fh) of lattice positions with the owned free nodes at [ex0, ex0 + w) x [ey0, ey0 + h)
+// and padded (0, 0) on a cell corner; every position outside the owned rectangle is a ghost with id Np + ring index
+// (arithmetic, see ring_index), filled by ONE halo exchange from whichever rank owns that position modulo the period
+// (possibly this rank itself).  A ring of depth D lets the whole preconditioner + operator chain of a GMRES iteration run
+// on local data with shrinking validity: 14 -> 1 exchanges per iteration.
+struct Ring
+{
+  bool active = false;
+  int32_t D = 0;                      // requested depth (every margin is >= D)
+  int32_t ex0 = 0, ey0 = 0, fw = 0, fh = 0, ncx = 0, ncy = 0; // padded geometry (replaces the frame of Lattice)
+  int64_t n_ring = 0;                 // fw fh - w h ring positions (+ 1 scratch slot at index n_ring)
+  std::vector<int32_t> self_src, self_dst; // ring positions owned by this rank itself: tail[self_dst] = owned[self_src]
+  std::vector<int32_t> recv_pos;      // [recv_ptr.back()] ring index of the k-th received value (peer-major order)
+};
+
+inline int64_t ring_index(int32_t X, int32_t Y, int32_t ex0, int32_t ey0, int32_t w, int32_t h, int32_t fw, int32_t fh)
+{
+  if (Y < ey0)
+    return (int64_t)Y * fw + X;
+  if (Y >= ey0 + h)
+    return (int64_t)(Y - h) * fw + X;
+  return (int64_t)(fh - h) * fw + (int64_t)(Y - ey0) * (fw - w) + (X < ex0 ? X : X - w);
+}
 
 enum
 {
@@ -92,6 +130,7 @@ struct Plan
   int64_t nnz_mono = 0;
   bool has_tables = true;               // SELL pattern + per-cell tables were built
   Lattice lat;
+  Ring ring;
   std::string error;
 };
 
@@ -102,6 +141,11 @@ int build_plan(const pfc_mesh &mesh, int degree, Plan &plan, int flags = 0);
 // uniform periodic tensor lattice with a rectangular owned region
 bool detect_lattice(const pfc_mesh &mesh, Plan &plan, const std::vector<int32_t> &cnode,
                     const std::vector<int32_t> &master, const std::vector<double> &h_of);
+// pfc_ring_plan.cpp: this rank's card, and the overlay that replaces the plan's one-cell ghost layer by the deep ring
+// (ghost ids, halo lists incl. self copies, slave masters, ghost_global for the handed-over frame nodes).
+// `cards` holds all ranks' cards in rank order.  Pure host code (CPU tests run it for every rank of a partition).
+RingCard ring_card(const Plan &plan);
+int ring_overlay(Plan &plan, const std::vector<RingCard> &cards, int depth);
 // built-in FE_Q(p) x QGauss(p+1) 1-D tables the lattice kernels are compiled with
 double lattice_shape_1d(int p, int q, int j);
 double lattice_dshape_1d(int p, int q, int j);

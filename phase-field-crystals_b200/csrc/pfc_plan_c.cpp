@@ -116,4 +116,58 @@ extern "C" int pfc_plan_monolithic(const pfc_plan *p, int64_t *row_ptr, int32_t 
   return PFC_OK;
 }
 
+// all ranks of a partition in one process (CPU tests): gather the cards, overlay every plan
+extern "C" int pfc_plan_ring_overlay(pfc_plan *const *plans, int32_t n_ranks, int32_t depth, char *err, int32_t err_len)
+{
+  if (!plans || n_ranks < 1)
+    return PFC_ERR_BAD_ARGUMENT;
+  std::vector<pfc::RingCard> cards;
+  for (int r = 0; r < n_ranks; ++r)
+    {
+      if (!plans[r] || plans[r]->P.rank != r || plans[r]->P.n_ranks != n_ranks)
+        return PFC_ERR_BAD_ARGUMENT;
+      cards.push_back(pfc::ring_card(plans[r]->P));
+    }
+  for (int r = 0; r < n_ranks; ++r)
+    {
+      const int rc = pfc::ring_overlay(plans[r]->P, cards, depth);
+      if (rc != PFC_OK)
+        {
+          if (err && err_len > 0)
+            std::snprintf(err, (size_t)err_len, "rank %d: %s", r, plans[r]->P.error.c_str());
+          return rc;
+        }
+    }
+  return PFC_OK;
+}
+
+extern "C" void pfc_plan_get_ring(const pfc_plan *p, pfc_ring_view *v)
+{
+  if (!p || !v)
+    return;
+  const pfc::Plan &P = p->P;
+  const pfc::Ring &R = P.ring;
+  std::memset(v, 0, sizeof(*v));
+  v->active = R.active ? 1 : 0;
+  v->depth = R.D;
+  v->ex0 = R.ex0;
+  v->ey0 = R.ey0;
+  v->fw = R.fw;
+  v->fh = R.fh;
+  v->ncx = R.ncx;
+  v->ncy = R.ncy;
+  v->n_ring = R.n_ring;
+  v->n_self = (int64_t)R.self_src.size();
+  v->n_recv = (int64_t)R.recv_pos.size();
+  v->n_send = (int64_t)P.send_rows.size();
+  v->n_peers = (int64_t)P.peers.size();
+  v->self_src = R.self_src.data();
+  v->self_dst = R.self_dst.data();
+  v->recv_pos = R.recv_pos.data();
+  v->send_rows = P.send_rows.data();
+  v->peers = P.peers.data();
+  v->recv_ptr = P.recv_ptr.data();
+  v->send_ptr = P.send_ptr.data();
+}
+
 extern "C" void pfc_plan_destroy(pfc_plan *p) { delete p; }

@@ -1,6 +1,7 @@
 // pfc_precond.cu — host drivers of the block-Schur right preconditioner (kernels: pfc_precond.cuh).
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <vector>
 
 #include "pfc_comm.h"
@@ -41,23 +42,10 @@ static inline int vgrid(const pfc_handle *h, int64_t n)
   return (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, (int64_t)h->n_sm * 8));
 }
 
-// K / B-C-D products: SELL kernels on the assembled blocks, or the matrix-free lattice cell kernel
+// K / B-C-D products of the assembled path (the lattice path runs precond_apply_ring below)
 static void run_kmv(pfc_handle *h, const SellArgs &S, int nb, const double *add, double a, const double *v, double k,
                     double *out, double *out2, const Ctl *ctl)
 {
-  if (h->lat)
-    {
-      LatOp op = lat_op(h);
-      op.s0 = v;
-      op.add = add;
-      op.a = a;
-      op.k = k;
-      op.out = out;
-      op.out2 = out2;
-      lat_launch(h, LAT_K, op, ctl);
-      h->launches--; // counted by the caller
-      return;
-    }
   kmv_kernel<<<nb, kSpmvThreads, 0, h->stream>>>(S, add, a, v, k, h->d_inv_ml.p, out, out2, ctl);
 }
 
@@ -66,26 +54,6 @@ static void run_bcd(pfc_handle *h, const SellArgs &S, int nb, const double *v0, 
                     double sB, double sC, double sD, const double *add, const double *dinv, double *d,
                     const double *cheb, double *out, const Ctl *ctl)
 {
-  if (h->lat)
-    {
-      LatOp op = lat_op(h);
-      op.in3b = h->d_psi_n.p;
-      op.s0 = v0;
-      op.s1 = v1;
-      op.s2 = v2;
-      op.sB = sB;
-      op.sC = sC;
-      op.sD = sD;
-      op.add = add;
-      op.dinv = dinv;
-      op.d = d;
-      op.cheb = cheb;
-      op.out = out;
-      op.epi = MODE;
-      lat_launch(h, LAT_S, op, ctl);
-      h->launches--; // counted by the caller
-      return;
-    }
   bcd_kernel<MODE><<<nb, kSpmvThreads, 0, h->stream>>>(S, v0, v1, v2, sB, sC, sD, add, dinv, d, cheb, out, ctl);
 }
 
@@ -121,6 +89,20 @@ int precond_after_setup(pfc_handle *h)
 // y = diag(B)^-1 S_L v   (scalar fields), the operator whose spectrum the Chebyshev interval must cover
 static int apply_dinv_SL(pfc_handle *h, double *v, double *y)
 {
+  if (h->lat)
+    { // the smoother's operator on the lattice path is the constant-coefficient S~ (pfc_ring.cuh)
+      PFC_TRY(halo_exchange_scalar(h, v));
+      RingOp o;
+      std::memset(&o, 0, sizeof(o));
+      o.x = v;
+      o.dinv = h->d_dinvB.p;
+      o.out = y;
+      o.bbar = 1.0;
+      o.dtth = h->prm.dt * h->prm.theta;
+      o.lo = 3 * h->plan.degree;
+      o.epi = 2;
+      return ring_launch_sweep(h, o, nullptr);
+    }
   const SellArgs S = sell_args(h);
   const int nb = sell_blocks(h);
   cudaStream_t s = h->stream;
@@ -160,6 +142,8 @@ int precond_refresh(pfc_handle *h)
       rowdiag_kernel<false><<<sell_blocks(h), kSpmvThreads, 0, s>>>(sell_args(h), h->d_dinvB.p);
       h->launches++;
     }
+  else
+    PFC_TRY(halo_exchange_scalar(h, h->d_dinvB.p)); // the sweeps run on the ring too
   const bool estimate = !h->eig_valid || h->solves_since_eig >= 16;
   if (estimate)
     {
@@ -217,9 +201,96 @@ int precond_refresh(pfc_handle *h)
   return PFC_OK;
 }
 
-// out = P^-1 in   (in, out: solver vectors of 3 components; stream-ordered, graph-capturable)
-int precond_apply(pfc_handle *h, const double *in, double *out, const Ctl *ctl)
+// scalar field [owned | ring] -> component 0 of a 3-component vector (only needed when there is a single sweep)
+static __global__ void ring_to_vec0_kernel(double *__restrict__ out, const double *__restrict__ x, int64_t n, int64_t Np,
+                                           const Ctl *ctl)
 {
+  if (ctl && ctl->state != 0)
+    return;
+  for (int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; u < n; u += (int64_t)gridDim.x * blockDim.x)
+    out[u < Np ? u : 3 * u] = x[u];
+}
+
+// Lattice path: the whole application on the ring overlay, ONE halo exchange (of `in`), then local kernels on windows that
+// shrink by the reach of every stage (margins in nodes, p = degree, s = sweeps):
+//   t kernel p | Schur right-hand side + first Chebyshev step 2p | sweep i 2p + 3p i | back substitution 3p s + p
+// so that out = (psi, chi, phi) is valid one cell beyond the owned nodes and the operator needs no exchange of its own
+// (ring depth (3 s + 2) p, pfc_api.cu).
+static int precond_apply_ring(pfc_handle *h, double *in, double *out, const Ctl *ctl)
+{
+  const Plan &P = h->plan;
+  const int p = P.degree, sw = h->sweeps;
+  double *m1 = wv(h, W_M1), *t = wv(h, W_T), *rhs = wv(h, W_RHS), *xa = wv(h, W_XA), *xb = wv(h, W_XB), *d = wv(h, W_D);
+  PFC_TRY(halo_exchange(h, in, ctl));
+  RingOp a;
+  std::memset(&a, 0, sizeof(a));
+  a.in = in;
+  a.t = t;
+  a.m1 = m1;
+  a.lo = p;
+  PFC_TRY(ring_launch_t(h, a, ctl));
+  {
+    LatOp op = lat_op(h); // rhs = r0 - C m1 - D t (exact, iterate-dependent C), d = x = dinv rhs / theta
+    op.in3b = h->d_psi_n.p;
+    op.s1 = m1;
+    op.s2 = t;
+    op.sB = 0.0;
+    op.sC = -1.0;
+    op.sD = -1.0;
+    op.add = in;
+    op.add_c = 0;
+    op.dinv = h->d_dinvB.p;
+    op.cheb = h->d_cheb.p;
+    op.d = d;
+    op.out = rhs;
+    op.out2 = xa;
+    op.epi = 0;
+    op.lo = 2 * p;
+    PFC_TRY(lat_launch(h, LAT_S, op, ctl));
+  }
+  double *x = xa, *xn = xb;
+  for (int i = 1; i < sw; ++i)
+    {
+      RingOp o;
+      std::memset(&o, 0, sizeof(o));
+      o.x = x;
+      o.rhs = rhs;
+      o.dinv = h->d_dinvB.p;
+      o.cheb = h->d_cheb.p + 2 * i;
+      o.d = d;
+      o.bbar = 1.0;
+      o.dtth = h->prm.dt * h->prm.theta;
+      o.lo = 2 * p + 3 * p * i;
+      o.epi = 0;
+      if (i == sw - 1)
+        o.out = out, o.out_vec = 1; // the last sweep writes psi straight into the result vector
+      else
+        o.out = xn;
+      PFC_TRY(ring_launch_sweep(h, o, ctl));
+      std::swap(x, xn);
+    }
+  if (sw == 1)
+    {
+      const int64_t n = P.Np + P.n_ghost;
+      ring_to_vec0_kernel<<<vgrid(h, n), 256, 0, h->stream>>>(out, xa, n, P.Np, ctl);
+      h->launches++;
+    }
+  RingOp b;
+  std::memset(&b, 0, sizeof(b));
+  b.in = in;
+  b.z = out;
+  b.lo = 3 * p * sw + p;
+  PFC_TRY(ring_launch_back(h, b, ctl));
+  PFC_CUDA(h, cudaGetLastError());
+  return PFC_OK;
+}
+
+// out = P^-1 in   (in, out: solver vectors of 3 components; stream-ordered, graph-capturable).  Lattice path: the ring
+// of `in` is refreshed here and out is valid one cell beyond the owned nodes.
+int precond_apply(pfc_handle *h, double *in, double *out, const Ctl *ctl)
+{
+  if (h->lat)
+    return precond_apply_ring(h, in, out, ctl);
   const Plan &P = h->plan;
   const SellArgs S = sell_args(h);
   const int nb = sell_blocks(h), g = vgrid(h, P.Np);
@@ -235,42 +306,13 @@ int precond_apply(pfc_handle *h, const double *in, double *out, const Ctl *ctl)
   run_kmv(h, S, nb, r2, 1.0, m1, -1.0, t, nullptr, ctl);                // t = M_L^-1 (r2 - K m1)
   PFC_TRY(halo_exchange_scalar(h, t, ctl));
   // Schur right-hand side rhs = r0 - C m1 - D t, then Chebyshev on S_L psi = rhs with Jacobi scaling diag(B)^-1:
-  // first step d = x = dinv rhs / theta (fused into the epilogue of the lattice kernel)
-  if (h->lat)
-    {
-      LatOp op = lat_op(h);
-      op.in3b = h->d_psi_n.p;
-      op.s1 = m1;
-      op.s2 = t;
-      op.sB = 0.0;
-      op.sC = -1.0;
-      op.sD = -1.0;
-      op.add = r0;
-      op.dinv = h->d_dinvB.p;
-      op.cheb = h->d_cheb.p;
-      op.d = d;
-      op.out = rhs;
-      op.out2 = xa;
-      op.epi = 0;
-      PFC_TRY(lat_launch(h, LAT_S, op, ctl));
-      h->launches += 2;
-    }
-  else
-    {
-      run_bcd<0>(h, S, nb, nullptr, m1, t, 0.0, -1.0, -1.0, r0, nullptr, nullptr, nullptr, rhs, ctl);
-      vec_mul_kernel<<<g, 256, 0, s>>>(d, xa, 1.0, h->d_cheb.p, rhs, h->d_dinvB.p, Np, ctl);          // d = x = dinv rhs / theta
-      h->launches += 4;
-    }
+  // first step d = x = dinv rhs / theta
+  run_bcd<0>(h, S, nb, nullptr, m1, t, 0.0, -1.0, -1.0, r0, nullptr, nullptr, nullptr, rhs, ctl);
+  vec_mul_kernel<<<g, 256, 0, s>>>(d, xa, 1.0, h->d_cheb.p, rhs, h->d_dinvB.p, Np, ctl);          // d = x = dinv rhs / theta
+  h->launches += 4;
   double *x = xa, *xn = xb;
   for (int i = 1; i < h->sweeps; ++i)
     {
-      if (h->smoother_const)
-        { // EXPERIMENTAL: the sweep on S~ = M + D M_L^-1 K M_L^-1 K in one kernel
-          const SmoothOp so{x, rhs, h->d_dinvB.p, h->d_cheb.p + 2 * i, d, xn, 1.0, 0.0, h->prm.dt * h->prm.theta};
-          PFC_TRY(lat_smooth(h, so, ctl));
-          std::swap(x, xn);
-          continue;
-        }
       PFC_TRY(halo_exchange_scalar(h, x, ctl));
       run_kmv(h, S, nb, nullptr, 0.0, x, 1.0, t1, nullptr, ctl);
       PFC_TRY(halo_exchange_scalar(h, t1, ctl));
@@ -291,10 +333,10 @@ int precond_apply(pfc_handle *h, const double *in, double *out, const Ctl *ctl)
   return PFC_OK;
 }
 
-// bench.py roofline legs of the preconditioner (include/pfc_b200.h)
-extern "C" int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms3, double *bytes2)
+// bench.py roofline legs of the preconditioner (include/pfc_b200.h): ms5 / bytes4, see the header
+extern "C" int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms5, double *bytes4)
 {
-  if (!h || reps < 1 || !ms3)
+  if (!h || reps < 1 || !ms5)
     return PFC_ERR_BAD_ARGUMENT;
   if (!h->assembled || h->prm.preconditioner != PFC_PRECOND_BLOCK_SCHUR)
     return h->fail(PFC_ERR_STATE, "pfc_time_precond needs pfc_assemble and PFC_PRECOND_BLOCK_SCHUR");
@@ -302,13 +344,17 @@ extern "C" int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms3, double
   PFC_TRY(precond_refresh(h));
   const Plan &P = h->plan;
   const SellArgs S = sell_args(h);
-  const int nb = sell_blocks(h);
+  const int nb = sell_blocks(h), p = P.degree;
   cudaStream_t s = h->stream;
-  double *in = h->d_V.p, *t1 = wv(h, W_T1), *t2 = wv(h, W_T2), *x = wv(h, W_XA), *xn = wv(h, W_XB);
+  double *t1 = wv(h, W_T1), *t2 = wv(h, W_T2), *x = wv(h, W_XA), *xn = wv(h, W_XB);
+  const int n_legs = h->lat ? 5 : 3;
+  for (int i = 0; i < 5; ++i)
+    ms5[i] = 0;
   // each leg: `reps` launches captured in one CUDA graph (the solver runs its cycle as a graph too), so the
-  // number is device time per launch, not host launch rate
+  // number is device time per launch, not host launch rate; 3-component operands rotate through the Krylov basis
+  const int half = std::max(1, h->n_basis / 2);
   float ms;
-  for (int leg = 0; leg < 3; ++leg)
+  for (int leg = 0; leg < n_legs; ++leg)
     {
       cudaGraph_t graph = nullptr;
       cudaGraphExec_t exec = nullptr;
@@ -317,8 +363,41 @@ extern "C" int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms3, double
       int rc = PFC_OK;
       for (int i = 0; i < reps && rc == PFC_OK; ++i)
         {
+          double *in = h->d_V.p + (int64_t)(i % half) * h->stride, *out = h->d_V.p + (int64_t)(half + i % half) * h->stride;
           if (leg == 0)
             rc = precond_apply(h, in, h->d_z.p, nullptr);
+          else if (h->lat)
+            {
+              RingOp o;
+              std::memset(&o, 0, sizeof(o));
+              o.in = in;
+              o.bbar = 1.0;
+              o.dtth = h->prm.dt * h->prm.theta;
+              if (leg == 1)
+                {
+                  o.x = (i & 1) ? xn : x, o.out = (i & 1) ? x : xn, o.rhs = wv(h, W_RHS), o.dinv = h->d_dinvB.p;
+                  o.cheb = h->d_cheb.p + 2, o.d = wv(h, W_D), o.lo = 5 * p;
+                  rc = ring_launch_sweep(h, o, nullptr);
+                }
+              else if (leg == 2)
+                {
+                  LatOp op = lat_op(h);
+                  op.in3b = h->d_psi_n.p, op.s1 = wv(h, W_M1), op.s2 = wv(h, W_T), op.sC = -1.0, op.sD = -1.0;
+                  op.add = in, op.add_c = 0, op.dinv = h->d_dinvB.p, op.cheb = h->d_cheb.p, op.d = wv(h, W_D);
+                  op.out = wv(h, W_RHS), op.out2 = x, op.epi = 0, op.lo = 2 * p;
+                  rc = lat_launch(h, LAT_S, op, nullptr);
+                }
+              else if (leg == 3)
+                {
+                  o.t = wv(h, W_T), o.m1 = wv(h, W_M1), o.lo = p;
+                  rc = ring_launch_t(h, o, nullptr);
+                }
+              else
+                {
+                  o.z = out, o.lo = 3 * p * h->sweeps + p;
+                  rc = ring_launch_back(h, o, nullptr);
+                }
+            }
           else if (leg == 1)
             run_kmv(h, S, nb, nullptr, 0.0, x, 1.0, t1, nullptr, nullptr);
           else
@@ -342,13 +421,15 @@ extern "C" int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms3, double
       PFC_CUDA(h, cudaStreamSynchronize(s));
       cudaGraphExecDestroy(exec);
       PFC_CUDA(h, cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]));
-      ms3[leg] = ms / reps;
+      ms5[leg] = ms / reps;
     }
   PFC_CUDA(h, cudaGetLastError());
-  if (bytes2)
+  if (bytes4)
     {
-      bytes2[0] = h->lat ? lat_bytes(h, LAT_K) : 12.0 * (double)P.n_ent + 32.0 * (double)P.Np;
-      bytes2[1] = h->lat ? lat_bytes(h, LAT_S) : 36.0 * (double)P.n_ent + 64.0 * (double)P.Np;
+      bytes4[0] = h->lat ? lat_bytes(h, RING_SWEEP) : 12.0 * (double)P.n_ent + 32.0 * (double)P.Np;
+      bytes4[1] = h->lat ? lat_bytes(h, RING_RHS) : 36.0 * (double)P.n_ent + 64.0 * (double)P.Np;
+      bytes4[2] = h->lat ? lat_bytes(h, RING_T) : 0.0;
+      bytes4[3] = h->lat ? lat_bytes(h, RING_BACK) : 0.0;
     }
   return PFC_OK;
 }

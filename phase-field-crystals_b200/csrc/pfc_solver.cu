@@ -44,7 +44,7 @@ static void launch_asm_colors(pfc_handle *h, const AsmArgs &A)
 }
 
 int precond_refresh(pfc_handle *h);                                                    // pfc_precond.cu
-int precond_apply(pfc_handle *h, const double *in, double *out, const pfc::Ctl *ctl); // pfc_precond.cu
+int precond_apply(pfc_handle *h, double *in, double *out, const pfc::Ctl *ctl); // pfc_precond.cu
 
 static inline bool is_general_mf(const pfc_handle *h)
 {
@@ -161,9 +161,10 @@ static int launch_mf(pfc_handle *h, const double *x, double *y, const Ctl *ctl)
 }
 
 // y = J x with the halo of x refreshed first (multi-rank)
-static int apply_operator(pfc_handle *h, double *x, double *y, const Ctl *ctl)
+static int apply_operator(pfc_handle *h, double *x, double *y, const Ctl *ctl, bool halo = true)
 {
-  PFC_TRY(halo_exchange(h, x, ctl));
+  if (halo)
+    PFC_TRY(halo_exchange(h, x, ctl));
   if (h->lat)
     {
       LatOp op = lat_op(h);
@@ -254,7 +255,8 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0,
       if (precond)
         { // right preconditioning: w = J P^-1 v_inner
           PFC_TRY(precond_apply(h, V + (int64_t)inner * st, h->d_z.p, ctl));
-          PFC_TRY(apply_operator(h, h->d_z.p, w, ctl));
+          // lattice path: P^-1 v is already valid one cell beyond the owned nodes (ring overlay), no exchange
+          PFC_TRY(apply_operator(h, h->d_z.p, w, ctl, !h->lat));
         }
       else
         PFC_TRY(apply_operator(h, V + (int64_t)inner * st, w, ctl)); // A.vmult

@@ -390,7 +390,7 @@ extern "C" int pfc_standin_hexagonal_lattice(const pfc_standin *s, double A0, do
 // Voronoi grains (minimum-image distance to seeds[n][2], ties to the lowest index); grain g carries the cos-sum of
 // HexagonalLattice<dim>::value (hexagonal_lattice.cpp:52-77, no dislocations) in its own frame
 // p' = R(alpha_g)^T rho + o_g, rho = minimum-image displacement from the seed.  Same operations in the same order as
-// orc_polycrystal (oracle/pfc_oracle.c): the two are compared bit for bit (tests/test_plan_cpu.py).
+// the CPU checker's copy (test infrastructure): the two are compared bit for bit (tests/test_plan_cpu.py).
 extern "C" int pfc_standin_polycrystal(const pfc_standin *s, double A0, double psi0, int32_t n_grains, const double *seeds,
                                        const double *alpha, const double *offset, double *Psi)
 {

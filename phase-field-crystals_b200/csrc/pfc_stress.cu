@@ -258,10 +258,9 @@ static int stress_impl(pfc_handle *h, double eps, double tol, double *stress, in
       // the kernels themselves follow the device mask
       for (int k = 0; k < kPollEvery; ++k)
         {
-          if (P.n_ranks > 1)
-            for (int c = 0; c < 4; ++c)
-              if ((host.mask >> c) & 1)
-                PFC_TRY(halo_exchange_scalar(h, d + c * ss));
+          for (int c = 0; c < 4; ++c) // ring values of the search directions (single rank: periodic wrap-around copies)
+            if ((host.mask >> c) & 1)
+              PFC_TRY(halo_exchange_scalar(h, d + c * ss));
           LatOp o = lat_op(h);
           o.s0 = d;
           o.out = hh;
@@ -287,9 +286,8 @@ static int stress_impl(pfc_handle *h, double eps, double tol, double *stress, in
   for (int c = 0; c < 4; ++c)
     cg_iters[c] = host.iters[c];
   // constraints.distribute, then the API order
-  if (P.n_ranks > 1)
-    for (int c = 0; c < 4; ++c)
-      PFC_TRY(halo_exchange_scalar(h, x + c * ss));
+  for (int c = 0; c < 4; ++c)
+    PFC_TRY(halo_exchange_scalar(h, x + c * ss));
   const int64_t nsl = (int64_t)P.slave_id.size();
   if (nsl > 0)
     {
@@ -348,7 +346,8 @@ extern "C" int pfc_output(pfc_handle *h, const pfc_mesh *mesh, int32_t kind, con
             if (P.perm[r] >= 0)
               values[c * N + P.perm[r]] = dev[c * ss + r];
           for (int64_t g = 0; g < P.n_ghost; ++g)
-            values[c * N + P.ghost_global[g]] = dev[c * ss + Np + g];
+            if (P.ghost_global[g] >= 0) // ring overlay: ring positions beyond the handed-over cells have no global id
+              values[c * N + P.ghost_global[g]] = dev[c * ss + Np + g];
         }
     }
   else
@@ -365,7 +364,8 @@ extern "C" int pfc_output(pfc_handle *h, const pfc_mesh *mesh, int32_t kind, con
             if (P.perm[r] >= 0)
               values[c * N + P.perm[r]] = dev[c * Np + r];
           for (int64_t g = 0; g < P.n_ghost; ++g)
-            values[c * N + P.ghost_global[g]] = dev[3 * (Np + g) + c];
+            if (P.ghost_global[g] >= 0)
+              values[c * N + P.ghost_global[g]] = dev[3 * (Np + g) + c];
         }
     }
   static const char *const state_names[3] = {"psi", "chi", "phi"};

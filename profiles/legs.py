@@ -40,9 +40,9 @@ def main():
                "gmres_iters": [x["gmres_iters_total"] for x in st], "launches": st[-1]["kernel_launches"],
                "ms_solver": st[-1]["ms_solver"], "ms_assembly": st[-1]["ms_assembly"],
                "us_operator": 1e3 * ms_op, "gbs_operator": by_op / ms_op / 1e6,
-               "us_precond_apply": 1e3 * pc["ms_apply"], "us_kmv": 1e3 * pc["ms_kmv"],
-               "gbs_kmv": pc["bytes_kmv"] / pc["ms_kmv"] / 1e6, "us_schur_row": 1e3 * pc["ms_schur_row"],
-               "gbs_schur_row": pc["bytes_schur_row"] / pc["ms_schur_row"] / 1e6,
+               "us_precond_apply": 1e3 * pc["ms_apply"],
+               "us_precond_legs [sweep | rhs | t | back] (assembled: [K product | Schur row])": [1e3 * x for x in pc["ms"][1:]],
+               "gbs_precond_legs": [b / m / 1e6 if m > 0 else None for m, b in zip(pc["ms"][1:], pc["bytes"])],
                "us_multidot10": 1e3 * kr["ms_dot"], "us_multiaxpy10": 1e3 * kr["ms_axpy"],
                "us_assembly": 1e3 * ms_asm}
         print(json.dumps(out), flush=True)

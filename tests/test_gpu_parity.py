@@ -464,13 +464,14 @@ def test_shipped_toml_run_end_to_end(built, tmp_path):
     sim.close()
 
 
-@pytest.mark.skipif(__import__("os").environ.get("PFC_SMOOTHER") != "1",
-                    reason="experimental one-kernel smoother (DESIGN.md §9 item 2): run with PFC_SMOOTHER=1")
-@pytest.mark.parametrize("degree,n_refines", [(1, 6), (2, 5), (2, 7)])
-def test_experimental_smoother(built, degree, n_refines):
-    """First thing to run when the constant-coefficient smoother is taken up: the tiled kernel against the composition of
-    the existing stencil kernels, then a step against the oracle (the smoother changes the preconditioner, not the answer)."""
-    om, st, s, Psi = _setup(built, degree, n_refines, operator_kind=1, preconditioner=1)
+@pytest.mark.parametrize("degree,n_refines,sweeps", [(1, 6, 0), (2, 5, 0), (2, 7, 0), (1, 3, 2), (2, 2, 1), (1, 8, 4)])
+def test_ring_smoother_and_selfchecks(built, degree, n_refines, sweeps):
+    """The streaming Chebyshev sweep (csrc/pfc_ring.cuh) against the composition of the K-stencil and mass-stencil kernels;
+    the K stencil against the cell-quadrature form; on meshes smaller than the ring as well (the ring then wraps around
+    the period several times).  Then a step against the oracle: the smoother changes the preconditioner, not the answer."""
+    om, st, s, Psi = _setup(built, degree, n_refines, operator_kind=1, preconditioner=1, precond_sweeps=sweeps)
+    assert s.operator_info()[0] == built.OPERATOR_MATRIX_FREE
+    assert s.selfcheck() <= 1e-12
     assert s.selfcheck_smoother() <= 1e-12
     if n_refines <= 6:
         s.set_state(Psi, Psi)
@@ -478,7 +479,7 @@ def test_experimental_smoother(built, degree, n_refines):
         Pn, Pn1 = Psi.copy(), Psi.copy()
         o = om.newton_step(Pn, Pn1, DT, 1.0, EPS)
         assert g["status"] == 0 and o["status"] == 0 and _rel(s.get_state()[:om.N], Pn[:om.N]) <= 1e-9
-        print(f"smoother Q{degree} 2^{n_refines}: gmres {g['gmres_iters']}")
+        print(f"ring path Q{degree} 2^{n_refines} sweeps {sweeps}: gmres {g['gmres_iters']}")
     s.close()
 
 
