@@ -214,8 +214,8 @@ int ring_overlay(Plan &P, const std::vector<RingCard> &cards, int depth)
         if (lx >= 0 && lx < L.w && ly >= 0 && ly < L.h)
           continue;
         const int32_t id = L.lut[(size_t)fy * L.fw + fx];
-        const int32_t glob = id < P.Np ? P.perm[id] : P.ghost_global[id - P.Np];
-        gg[(size_t)ring_index(lx + g.ex0, ly + g.ey0, g.ex0, g.ey0, g.w, g.h, g.fw, g.fh)] = glob;
+        if (id >= P.Np) // periodic images of the rank's own nodes stay anonymous copies: their global id maps to the owned row
+          gg[(size_t)ring_index(lx + g.ex0, ly + g.ey0, g.ex0, g.ey0, g.w, g.h, g.fw, g.fh)] = P.ghost_global[id - P.Np];
       }
   P.ghost_global.swap(gg);
   P.n_ghost = Rg.n_ring + 1;

@@ -77,6 +77,7 @@ def test_ring_exchange_fills_every_position(built, degree, n_refines, n_ranks, d
         L = pl.lattice
         w, h, ex0, ey0, fw, fh = L["w"], L["h"], rg["ex0"], rg["ey0"], rg["fw"], rg["fh"]
         g0 = pl.perm[0]                                  # owned free node (0, 0)
+        own = pl.perm[:pl.n_owned]
         Y, X = np.meshgrid(np.arange(fh), np.arange(fw), indexing="ij")
         want = f[node_at[(iy[g0] + Y - ey0) % PY, (ix[g0] + X - ex0) % PX]]
         inside = (X >= ex0) & (X < ex0 + w) & (Y >= ey0) & (Y < ey0 + h)
@@ -90,11 +91,15 @@ def test_ring_exchange_fills_every_position(built, degree, n_refines, n_ranks, d
         gg = rg["ghost_global"]
         known = np.nonzero(gg >= 0)[0]
         assert len(known) > 0 or n_ranks == 1
+        assert not np.isin(gg[known], own).any()        # images of the rank's own nodes stay anonymous
         assert np.array_equal(loc[r][pl.Np + known], f[gg[known]])
         fx, fy = np.meshgrid(np.arange(L["fw"]), np.arange(L["fh"]))
         lx, ly = fx - L["ex0"], fy - L["ey0"]
         out = ~((lx >= 0) & (lx < w) & (ly >= 0) & (ly < h))
-        assert (gg[ring_index(lx[out] + ex0, ly[out] + ey0, ex0, ey0, w, h, fw, fh)] >= 0).all()
+        at = gg[ring_index(lx[out] + ex0, ly[out] + ey0, ex0, ey0, w, h, fw, fh)]
+        there = node_at[(iy[g0] + ly[out]) % PY, (ix[g0] + lx[out]) % PX]   # resolved node at the frame position
+        mine = np.isin(there, own)
+        assert np.array_equal(at[~mine], there[~mine]) and (at[mine] == -1).all()
         # owned slaves: internal ids after the free nodes, master value at the slave's own position
         sid, smas = rg["slave_id"], rg["slave_master"]
         assert np.array_equal(sid, np.arange(w * h, pl.n_owned))
