@@ -136,9 +136,13 @@ constexpr int kRingThreads = 128;
 // re-reads its 2 HY warm-up rows)
 int ring_rows_per_strip(const pfc_handle *h, int col_blocks, int rows)
 {
-  const int want = 8 * h->n_sm;
-  const int strips = std::max(1, want / std::max(1, col_blocks));
-  return std::min(256, std::max(16, (rows + strips - 1) / strips));
+  static const int forced = getenv("PFC_RING_RS") ? atoi(getenv("PFC_RING_RS")) : 0; // tuning aid
+  if (forced > 0)
+    return forced;
+  int rs = 64; // every strip repeats (2 stages + 2) p warm-up rows; measured on B200 (profiles/r02f_ring_tuning.log)
+  while (rs > 16 && (int64_t)col_blocks * ((rows + rs - 1) / rs) < 8 * (int64_t)h->n_sm)
+    rs /= 2;
+  return rs;
 }
 
 template <int STAGES, class K1, class K2>
@@ -161,18 +165,23 @@ int ring_launch(pfc_handle *h, RingOp op, const Ctl *ctl, K1 q1, K2 q2)
 }
 } // namespace
 
-int ring_launch_t(pfc_handle *h, const RingOp &op, const Ctl *ctl)
+// prefetch depth of the register rings: Q1 default per kernel, Q2 depth 1 (registers); PFC_RING_PF: tuning aid
+static int ring_pf(int dflt)
 {
-  return ring_launch<1>(h, op, ctl, ring_t_kernel<1, kRingThreads>, ring_t_kernel<2, kRingThreads>);
+  static const int forced = getenv("PFC_RING_PF") ? atoi(getenv("PFC_RING_PF")) : 0;
+  return forced > 0 ? forced : dflt;
 }
-int ring_launch_sweep(pfc_handle *h, const RingOp &op, const Ctl *ctl)
-{
-  return ring_launch<3>(h, op, ctl, ring_sweep_kernel<1, kRingThreads>, ring_sweep_kernel<2, kRingThreads>);
-}
-int ring_launch_back(pfc_handle *h, const RingOp &op, const Ctl *ctl)
-{
-  return ring_launch<2>(h, op, ctl, ring_back_kernel<1, kRingThreads>, ring_back_kernel<2, kRingThreads>);
-}
+#define PFC_RING_DISPATCH(STAGES, KERNEL, DFLT)                                                               \
+  switch (ring_pf(h->plan.degree == 1 ? DFLT : 1))                                                                                    \
+    {                                                                                                         \
+    case 1: return ring_launch<STAGES>(h, op, ctl, KERNEL<1, kRingThreads, 1>, KERNEL<2, kRingThreads, 1>);   \
+    case 2: return ring_launch<STAGES>(h, op, ctl, KERNEL<1, kRingThreads, 2>, KERNEL<2, kRingThreads, 2>);   \
+    default: return ring_launch<STAGES>(h, op, ctl, KERNEL<1, kRingThreads, 4>, KERNEL<2, kRingThreads, 4>);  \
+    }
+int ring_launch_t(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(1, ring_t_kernel, 2) }
+int ring_launch_sweep(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(3, ring_sweep_kernel, 2) }
+int ring_launch_back(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(2, ring_back_kernel, 1) }
+#undef PFC_RING_DISPATCH
 
 // nodes N = w h; every field is read once (the halo ring through L2) and every output written once
 double lat_bytes(const pfc_handle *h, int mode)

@@ -98,7 +98,7 @@ __device__ __forceinline__ void ring_ysum(const RingTab<P> &T, int row, const do
 }
 
 // ---- t kernel: m1 = M_L^-1 r1, t = M_L^-1 (r2 - K m1) on the window of margin lo -------------------------------
-template <int P, int NT>
+template <int P, int NT, int PF>
 static __global__ void __launch_bounds__(NT) ring_t_kernel(LatGeom L, RingOp O, const Ctl *ctl)
 {
   if (ctl && ctl->state != 0)
@@ -120,41 +120,60 @@ static __global__ void __launch_bounds__(NT) ring_t_kernel(LatGeom L, RingOp O, 
   for (int dd = 0; dd < NW; ++dd)
     kx[dd] = T.v[0][tx][dd], mx[dd] = T.v[1][tx][dd], rK[dd] = 0, rM[dd] = 0;
   const int n0 = Y0 - HX, n1 = Y1 - 1 + HX;
-  double r1n = (colok && n0 >= 0) ? O.in[ring_vaddr(L, X, n0, 1)] : 0.0;
-  for (int n = n0; n <= n1; ++n)
+  // operands are fetched PF rows ahead into a register ring, so that PF rows of loads are in flight per thread
+  struct Pre
+  {
+    double r1n, o_r1, o_r2;
+    bool wr;
+  };
+  auto fetch = [&](int n, Pre &q) {
+    q.r1n = (colok && n <= n1 && n < L.fh) ? O.in[ring_vaddr(L, X, n, 1)] : 0.0;
+    const int m = n - P;
+    q.wr = outcol && m >= Y0 && m < Y1;
+    q.o_r1 = q.o_r2 = 0.0;
+    if (q.wr)
+      {
+        q.o_r1 = O.in[ring_vaddr(L, X, m, 1)];
+        q.o_r2 = O.in[ring_vaddr(L, X, m, 2)];
+      }
+  };
+  Pre pre[PF];
+#pragma unroll
+  for (int j = 0; j < PF; ++j)
+    fetch(n0 + j, pre[j]);
+  for (int nb = n0; nb <= n1; nb += PF)
     {
-      const int par = (n - n0) & 1;
-      const double a0 = r1n * ring_iml<P>(L, X, n);
-      r1n = (colok && n + 1 <= n1 && n + 1 < L.fh) ? O.in[ring_vaddr(L, X, n + 1, 1)] : 0.0;
-      const int m = n - P;
-      const bool wr = outcol && m >= Y0 && m < Y1;
-      double o_r1 = 0, o_r2 = 0;
-      if (wr)
+#pragma unroll
+      for (int j = 0; j < PF; ++j)
         {
-          o_r1 = O.in[ring_vaddr(L, X, m, 1)];
-          o_r2 = O.in[ring_vaddr(L, X, m, 2)];
-        }
-      s_ex[par][tid + P] = a0;
-      __syncthreads();
-      double k, mm;
-      ring_xsum<P>(&s_ex[par][tid], kx, mx, k, mm);
-      ring_push(rK, k);
-      ring_push(rM, mm);
-      if (wr)
-        {
-          double Kv, Mv;
-          ring_ysum<P>(T, m, rK, rM, Kv, Mv);
-          const double il = ring_iml<P>(L, X, m);
-          const int64_t r = lat_id(L, X, m);
-          O.t[r] = il * (o_r2 - Kv);
-          O.m1[r] = il * o_r1;
+          const int n = nb + j;
+          if (n > n1)
+            break;
+          const Pre cur = pre[j];
+          fetch(n + PF, pre[j]);
+          const int par = (n - n0) & 1, m = n - P;
+          s_ex[par][tid + P] = cur.r1n * ring_iml<P>(L, X, n);
+          __syncthreads();
+          double k, mm;
+          ring_xsum<P>(&s_ex[par][tid], kx, mx, k, mm);
+          ring_push(rK, k);
+          ring_push(rM, mm);
+          if (cur.wr)
+            {
+              double Kv, Mv;
+              ring_ysum<P>(T, m, rK, rM, Kv, Mv);
+              const double il = ring_iml<P>(L, X, m);
+              const int64_t r = lat_id(L, X, m);
+              O.t[r] = il * (cur.o_r2 - Kv);
+              O.m1[r] = il * cur.o_r1;
+            }
         }
     }
 }
 
 // ---- Chebyshev sweep on S~ -------------------------------------------------------------------------------------
 // epi 0: d = c0 d + c1 dinv (rhs - S~ x), out = x + d;  epi 2: out = dinv S~ x (power iteration);  epi 3: out = S~ x
-template <int P, int NT>
+template <int P, int NT, int PF>
 static __global__ void __launch_bounds__(NT) ring_sweep_kernel(LatGeom L, RingOp O, const Ctl *ctl)
 {
   if (ctl && ctl->state != 0)
@@ -186,63 +205,84 @@ static __global__ void __launch_bounds__(NT) ring_sweep_kernel(LatGeom L, RingOp
     c0 = O.cheb[0], c1 = O.cheb[1];
   auto ldx = [&](int Y) { return O.x[O.x_vec ? ring_vaddr(L, X, Y, 0) : lat_id(L, X, Y)]; };
   const int n0 = Y0 - HX, nx1 = Y1 - 1 + HX, n1 = nx1 + 2; // last x row needed; last iteration (output row Y1 - 1)
-  double xn = (colok && n0 >= 0) ? ldx(n0) : 0.0, a1 = 0, a2 = 0;
-  for (int n = n0; n <= n1; ++n)
+  struct Pre
+  {
+    double x, rhs, dinv, d, xo;
+    int32_t r;
+    bool wr;
+  };
+  auto fetch = [&](int n, Pre &q) {
+    q.x = (colok && n <= nx1 && n < L.fh) ? ldx(n) : 0.0;
+    const int m = n - 2 - 3 * P; // output row of iteration n
+    q.wr = outcol && m >= Y0 && m < Y1;
+    q.rhs = q.dinv = q.d = q.xo = 0.0;
+    q.r = 0;
+    if (q.wr)
+      {
+        q.r = lat_id(L, X, m);
+        if (O.epi == 0)
+          q.rhs = O.rhs[q.r], q.d = O.d[q.r], q.xo = ldx(m);
+        if (O.epi != 3)
+          q.dinv = O.dinv[q.r];
+      }
+  };
+  Pre pre[PF];
+#pragma unroll
+  for (int j = 0; j < PF; ++j)
+    fetch(n0 + j, pre[j]);
+  double a1 = 0, a2 = 0;
+  for (int nb = n0; nb <= n1; nb += PF)
     {
-      const int par = (n - n0) & 1;
-      const double a0 = xn;
-      xn = (colok && n + 1 <= nx1 && n + 1 < L.fh) ? ldx(n + 1) : 0.0;
-      const int m = n - 2 - 3 * P; // output row of this iteration
-      const bool wr = outcol && m >= Y0 && m < Y1;
-      double o_rhs = 0, o_dinv = 0, o_d = 0, o_x = 0;
-      int64_t r = 0;
-      if (wr)
+#pragma unroll
+      for (int j = 0; j < PF; ++j)
         {
-          r = lat_id(L, X, m);
-          if (O.epi == 0)
-            o_rhs = O.rhs[r], o_d = O.d[r], o_x = ldx(m);
-          if (O.epi != 3)
-            o_dinv = O.dinv[r];
-        }
-      s_ex[par][0][tid + P] = a0;
-      s_ex[par][1][tid + P] = a1;
-      s_ex[par][2][tid + P] = a2;
-      __syncthreads();
-      double k, mm, Kv, Mv;
-      ring_xsum<P>(&s_ex[par][0][tid], kx, mx, k, mm); // x, row n
-      ring_push(r1K, k);
-      ring_push(r1M, mm);
-      ring_xsum<P>(&s_ex[par][1][tid], kx, mx, k, mm); // t1, row n - 1 - p
-      ring_push(r2K, k);
-      ring_push(r2M, mm);
-      ring_xsum<P>(&s_ex[par][2][tid], kx, mx, k, mm); // t2, row n - 2 - 2p
-      ring_push(r3K, k);
-      ring_push(r3M, mm);
-      ring_ysum<P>(T, n - P, r1K, r1M, Kv, Mv); // t1 = M_L^-1 K x at row n - p; (M x) kept for the output row
-      a1 = Kv * ring_iml<P>(L, X, n - P);
-      ring_push(mxd, Mv);
-      ring_ysum<P>(T, n - 1 - 2 * P, r2K, r2M, Kv, Mv); // t2 = M_L^-1 K t1 at row n - 1 - 2p
-      a2 = Kv * ring_iml<P>(L, X, n - 1 - 2 * P);
-      if (wr)
-        {
-          ring_ysum<P>(T, m, r3K, r3M, Kv, Mv); // K t2, M t2 at the output row
-          const double Sx = O.bbar * mxd[0] + O.dtth * (Kv - 2.0 * Mv);
-          double res;
-          if (O.epi == 0)
+          const int n = nb + j;
+          if (n > n1)
+            break;
+          const Pre cur = pre[j];
+          fetch(n + PF, pre[j]);
+          const int par = (n - n0) & 1, m = n - 2 - 3 * P;
+          s_ex[par][0][tid + P] = cur.x;
+          s_ex[par][1][tid + P] = a1;
+          s_ex[par][2][tid + P] = a2;
+          __syncthreads();
+          double k, mm, Kv, Mv;
+          ring_xsum<P>(&s_ex[par][0][tid], kx, mx, k, mm); // x, row n
+          ring_push(r1K, k);
+          ring_push(r1M, mm);
+          ring_xsum<P>(&s_ex[par][1][tid], kx, mx, k, mm); // t1, row n - 1 - p
+          ring_push(r2K, k);
+          ring_push(r2M, mm);
+          ring_xsum<P>(&s_ex[par][2][tid], kx, mx, k, mm); // t2, row n - 2 - 2p
+          ring_push(r3K, k);
+          ring_push(r3M, mm);
+          ring_ysum<P>(T, n - P, r1K, r1M, Kv, Mv); // t1 = M_L^-1 K x at row n - p; (M x) kept for the output row
+          a1 = Kv * ring_iml<P>(L, X, n - P);
+          ring_push(mxd, Mv);
+          ring_ysum<P>(T, n - 1 - 2 * P, r2K, r2M, Kv, Mv); // t2 = M_L^-1 K t1 at row n - 1 - 2p
+          a2 = Kv * ring_iml<P>(L, X, n - 1 - 2 * P);
+          if (cur.wr)
             {
-              const double dn = c0 * o_d + c1 * o_dinv * (o_rhs - Sx);
-              O.d[r] = dn;
-              res = o_x + dn;
+              ring_ysum<P>(T, m, r3K, r3M, Kv, Mv); // K t2, M t2 at the output row
+              const double Sx = O.bbar * mxd[0] + O.dtth * (Kv - 2.0 * Mv);
+              const int64_t r = cur.r;
+              double res;
+              if (O.epi == 0)
+                {
+                  const double dn = c0 * cur.d + c1 * cur.dinv * (cur.rhs - Sx);
+                  O.d[r] = dn;
+                  res = cur.xo + dn;
+                }
+              else
+                res = O.epi == 2 ? cur.dinv * Sx : Sx;
+              O.out[O.out_vec ? (r < L.Np ? r : 3 * r) : r] = res;
             }
-          else
-            res = O.epi == 2 ? o_dinv * Sx : Sx;
-          O.out[O.out_vec ? (r < L.Np ? r : 3 * r) : r] = res;
         }
     }
 }
 
 // ---- back substitution: chi = M_L^-1 (r1 - K psi), phi = M_L^-1 (r2 - K chi); psi = component 0 of z -------------
-template <int P, int NT>
+template <int P, int NT, int PF>
 static __global__ void __launch_bounds__(NT) ring_back_kernel(LatGeom L, RingOp O, const Ctl *ctl)
 {
   if (ctl && ctl->state != 0)
@@ -267,34 +307,54 @@ static __global__ void __launch_bounds__(NT) ring_back_kernel(LatGeom L, RingOp 
       r1K[dd] = r1M[dd] = r2K[dd] = r2M[dd] = 0;
     }
   const int n0 = Y0 - HX, nx1 = Y1 - 1 + HX, n1 = nx1 + 1;
-  double xn = (colok && n0 >= 0) ? O.z[ring_vaddr(L, X, n0, 0)] : 0.0, a1 = 0;
-  for (int n = n0; n <= n1; ++n)
+  struct Pre
+  {
+    double x, o_r1, o_r2;
+    bool chi_ok, wr;
+  };
+  auto fetch = [&](int n, Pre &q) {
+    q.x = (colok && n <= nx1 && n < L.fh) ? O.z[ring_vaddr(L, X, n, 0)] : 0.0;
+    const int mc = n - P, m = n - 1 - 2 * P; // rows of chi / phi produced in iteration n
+    q.chi_ok = colok && mc >= 0 && mc < L.fh && n <= n1;
+    q.wr = outcol && m >= Y0 && m < Y1;
+    q.o_r1 = q.chi_ok ? O.in[ring_vaddr(L, X, mc, 1)] : 0.0;
+    q.o_r2 = q.wr ? O.in[ring_vaddr(L, X, m, 2)] : 0.0;
+  };
+  Pre pre[PF];
+#pragma unroll
+  for (int j = 0; j < PF; ++j)
+    fetch(n0 + j, pre[j]);
+  double a1 = 0;
+  for (int nb = n0; nb <= n1; nb += PF)
     {
-      const int par = (n - n0) & 1;
-      const double a0 = xn;
-      xn = (colok && n + 1 <= nx1 && n + 1 < L.fh) ? O.z[ring_vaddr(L, X, n + 1, 0)] : 0.0;
-      const int mc = n - P, m = n - 1 - 2 * P; // rows of chi / phi produced in this iteration
-      const bool chi_ok = colok && mc >= 0 && mc < L.fh, wr = outcol && m >= Y0 && m < Y1;
-      const double o_r1 = chi_ok ? O.in[ring_vaddr(L, X, mc, 1)] : 0.0;
-      const double o_r2 = wr ? O.in[ring_vaddr(L, X, m, 2)] : 0.0;
-      s_ex[par][0][tid + P] = a0;
-      s_ex[par][1][tid + P] = a1;
-      __syncthreads();
-      double k, mm, Kv, Mv;
-      ring_xsum<P>(&s_ex[par][0][tid], kx, mx, k, mm); // psi, row n
-      ring_push(r1K, k);
-      ring_push(r1M, mm);
-      ring_xsum<P>(&s_ex[par][1][tid], kx, mx, k, mm); // chi, row n - 1 - p
-      ring_push(r2K, k);
-      ring_push(r2M, mm);
-      ring_ysum<P>(T, mc, r1K, r1M, Kv, Mv);
-      a1 = chi_ok ? ring_iml<P>(L, X, mc) * (o_r1 - Kv) : 0.0;
-      if (outcol && mc >= Y0 && mc < Y1)
-        O.z[ring_vaddr(L, X, mc, 1)] = a1;
-      if (wr)
+#pragma unroll
+      for (int j = 0; j < PF; ++j)
         {
-          ring_ysum<P>(T, m, r2K, r2M, Kv, Mv);
-          O.z[ring_vaddr(L, X, m, 2)] = ring_iml<P>(L, X, m) * (o_r2 - Kv);
+          const int n = nb + j;
+          if (n > n1)
+            break;
+          const Pre cur = pre[j];
+          fetch(n + PF, pre[j]);
+          const int par = (n - n0) & 1, mc = n - P, m = n - 1 - 2 * P;
+          s_ex[par][0][tid + P] = cur.x;
+          s_ex[par][1][tid + P] = a1;
+          __syncthreads();
+          double k, mm, Kv, Mv;
+          ring_xsum<P>(&s_ex[par][0][tid], kx, mx, k, mm); // psi, row n
+          ring_push(r1K, k);
+          ring_push(r1M, mm);
+          ring_xsum<P>(&s_ex[par][1][tid], kx, mx, k, mm); // chi, row n - 1 - p
+          ring_push(r2K, k);
+          ring_push(r2M, mm);
+          ring_ysum<P>(T, mc, r1K, r1M, Kv, Mv);
+          a1 = cur.chi_ok ? ring_iml<P>(L, X, mc) * (cur.o_r1 - Kv) : 0.0;
+          if (outcol && mc >= Y0 && mc < Y1)
+            O.z[ring_vaddr(L, X, mc, 1)] = a1;
+          if (cur.wr)
+            {
+              ring_ysum<P>(T, m, r2K, r2M, Kv, Mv);
+              O.z[ring_vaddr(L, X, m, 2)] = ring_iml<P>(L, X, m) * (cur.o_r2 - Kv);
+            }
         }
     }
 }
