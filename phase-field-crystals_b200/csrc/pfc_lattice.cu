@@ -165,22 +165,20 @@ int ring_launch(pfc_handle *h, RingOp op, const Ctl *ctl, K1 q1, K2 q2)
 }
 } // namespace
 
-// prefetch depth of the register rings: Q1 default per kernel, Q2 depth 1 (registers); PFC_RING_PF: tuning aid
-static int ring_pf(int dflt)
+// prefetch depth of the register rings: 1 row, or (deep) one turn of the row phase = 2p + 1 rows; PFC_RING_PF=1|2 forces
+// shallow | deep (tuning aid)
+static bool ring_deep(bool dflt)
 {
   static const int forced = getenv("PFC_RING_PF") ? atoi(getenv("PFC_RING_PF")) : 0;
-  return forced > 0 ? forced : dflt;
+  return forced > 0 ? forced > 1 : dflt;
 }
-#define PFC_RING_DISPATCH(STAGES, KERNEL, DFLT)                                                               \
-  switch (ring_pf(h->plan.degree == 1 ? DFLT : 1))                                                                                    \
-    {                                                                                                         \
-    case 1: return ring_launch<STAGES>(h, op, ctl, KERNEL<1, kRingThreads, 1>, KERNEL<2, kRingThreads, 1>);   \
-    case 2: return ring_launch<STAGES>(h, op, ctl, KERNEL<1, kRingThreads, 2>, KERNEL<2, kRingThreads, 2>);   \
-    default: return ring_launch<STAGES>(h, op, ctl, KERNEL<1, kRingThreads, 4>, KERNEL<2, kRingThreads, 4>);  \
-    }
-int ring_launch_t(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(1, ring_t_kernel, 2) }
-int ring_launch_sweep(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(3, ring_sweep_kernel, 2) }
-int ring_launch_back(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(2, ring_back_kernel, 1) }
+#define PFC_RING_DISPATCH(STAGES, KERNEL, DEEP1, DEEP2)                                                         \
+  if (ring_deep(h->plan.degree == 1 ? DEEP1 : DEEP2))                                                           \
+    return ring_launch<STAGES>(h, op, ctl, KERNEL<1, kRingThreads, 3>, KERNEL<2, kRingThreads, 5>);             \
+  return ring_launch<STAGES>(h, op, ctl, KERNEL<1, kRingThreads, 1>, KERNEL<2, kRingThreads, 1>);
+int ring_launch_t(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(1, ring_t_kernel, true, false) }
+int ring_launch_sweep(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(3, ring_sweep_kernel, true, false) }
+int ring_launch_back(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(2, ring_back_kernel, false, false) }
 #undef PFC_RING_DISPATCH
 
 // nodes N = w h; every field is read once (the halo ring through L2) and every output written once

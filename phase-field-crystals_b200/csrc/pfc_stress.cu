@@ -368,6 +368,25 @@ extern "C" int pfc_output(pfc_handle *h, const pfc_mesh *mesh, int32_t kind, con
               values[c * N + P.ghost_global[g]] = dev[3 * (Np + g) + c];
         }
     }
+  // slaves of other ranks that sit on this rank's cells (ring overlay: a ring position carries the id of the node it
+  // resolves to, not the slave's): constraints.distribute on the host, value of the master (mpi.cpp:609, stress.cpp:366)
+  if (kind != 1)
+    {
+      std::vector<char> known((size_t)N, 0);
+      for (int64_t r = 0; r < Np; ++r)
+        if (P.perm[r] >= 0)
+          known[P.perm[r]] = 1;
+      for (int64_t g = 0; g < P.n_ghost; ++g)
+        if (P.ghost_global[g] >= 0)
+          known[P.ghost_global[g]] = 1;
+      for (int64_t k = 0; k < mesh->n_constraints; ++k)
+        {
+          const int64_t sl = mesh->constraint_slave[k], ms = mesh->constraint_master[k];
+          if (sl < N && ms < N && !known[sl] && known[ms])
+            for (int c = 0; c < nf; ++c)
+              values[c * N + sl] = values[c * N + ms];
+        }
+    }
   static const char *const state_names[3] = {"psi", "chi", "phi"};
   static const char *const stress_names[4] = {"stress", "stress", "stress", "stress"};
   static const int32_t scalar3[3] = {0, 0, 0}, tensor4[4] = {1, 1, 1, 1};

@@ -1,7 +1,7 @@
 #!/bin/bash
-# tuning aid: legs of the ring path for prefetch depth / rows per strip (PFC_RING_PF, PFC_RING_RS)
+# tuning aid: legs of the ring path for prefetch depth (PFC_RING_PF: 1 shallow, 2 deep) / rows per strip (PFC_RING_RS)
 for wl in "--degree 1 --n-refines 12 --sweeps 3" "--degree 2 --n-refines 9 --sweeps 5"; do
-  for pf in 1 2 4; do for rs in 16 32 64 128; do
+  for pf in ${PFS:-1 2}; do for rs in ${RSS:-16 32 64 128}; do
     echo "== $wl pf=$pf rs=$rs"
     PFC_RING_PF=$pf PFC_RING_RS=$rs python profiles/legs.py $wl --steps 1 2>&1 | python -c "
 import sys, json
