@@ -206,6 +206,11 @@ int pfc_selfcheck(pfc_handle *h, double *max_rel);
 /* lattice path with the preconditioner: S~ x by the one-kernel streaming Chebyshev sweep (csrc/pfc_ring.cuh) against the
  * composition of the K-stencil and mass-stencil kernels with a halo exchange before every product [collective] */
 int pfc_selfcheck_smoother(pfc_handle *h, double *max_rel);
+/* Q1 lattice path: the closed-form kernels (csrc/pfc_ring_q1.cuh: J apply with the constant blocks as stencils; t kernel +
+ * Schur right-hand side fused; sweeps, back substitution) against the general kernels they replace, on a pseudo-random
+ * vector: max_rel2[0] J apply, max_rel2[1] preconditioner application; max |a - b| / max |b| over the owned rows.  Needs
+ * pfc_assemble and PFC_PRECOND_BLOCK_SCHUR.  [collective] */
+int pfc_selfcheck_q1(pfc_handle *h, double *max_rel2);
 /* which operator path pfc_setup chose: returns PFC_OPERATOR_ASSEMBLED, PFC_OPERATOR_MATRIX_FREE (lattice kernels) or
  * PFC_OPERATOR_MATRIX_FREE_GENERAL, -1 before pfc_setup; note (optional) receives why the lattice kernels were declined
  * when PFC_OPERATOR_MATRIX_FREE was asked for and the general kernel is in charge (empty otherwise) */

@@ -112,7 +112,7 @@ EXPORTED_SYMBOLS = [
     "pfc_nccl_unique_id", "pfc_comm_init", "pfc_comm_mode", "pfc_time_comm", "pfc_set_state", "pfc_get_state", "pfc_n_owned_nodes", "pfc_set_state_owned", "pfc_get_state_owned", "pfc_assemble",
     "pfc_residual_norm", "pfc_solve_update", "pfc_step", "pfc_run", "pfc_get_rhs", "pfc_get_nnz",
     "pfc_get_pattern", "pfc_get_matrix_values", "pfc_apply_operator", "pfc_get_dof_permutation",
-    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_selfcheck_smoother", "pfc_stress", "pfc_stress_owned", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
+    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_selfcheck_smoother", "pfc_selfcheck_q1", "pfc_stress", "pfc_stress_owned", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
     "pfc_standin_create_ex", "pfc_standin_destroy",
     "pfc_standin_mesh", "pfc_standin_n_nodes", "pfc_standin_support_points",
     "pfc_standin_hexagonal_lattice", "pfc_standin_polycrystal", "pfc_plan_build", "pfc_plan_build_ex", "pfc_plan_get_lattice", "pfc_plan_ring_overlay", "pfc_plan_get_ring", "pfc_operator_info", "pfc_plan_get_view", "pfc_plan_monolithic",
@@ -185,6 +185,7 @@ def lib():
     L.pfc_time_precond.argtypes = [hp, C.c_int32, _f64p, _f64p]
     L.pfc_selfcheck.argtypes = [hp, _f64p]
     L.pfc_selfcheck_smoother.argtypes = [hp, _f64p]
+    L.pfc_selfcheck_q1.argtypes = [hp, _f64p]
     L.pfc_n_owned_nodes.argtypes = [hp]
     L.pfc_n_owned_nodes.restype = C.c_int64
     L.pfc_set_state_owned.argtypes = [hp, _f64p, _f64p]
@@ -572,6 +573,12 @@ class Solver:
         v = C.c_double()
         self._check(lib().pfc_selfcheck_smoother(self._h, C.byref(v)))
         return v.value
+
+    def selfcheck_q1(self):
+        """(J apply, preconditioner application): closed-form Q1 kernels against the general ones (pfc_selfcheck_q1)"""
+        v = (C.c_double * 2)()
+        self._check(lib().pfc_selfcheck_q1(self._h, v))
+        return v[0], v[1]
 
     def time_precond(self, reps=10):
         """legs of include/pfc_b200.h pfc_time_precond: ms[0..4], bytes[0..3] (bytes[k] belongs to ms[k + 1])"""

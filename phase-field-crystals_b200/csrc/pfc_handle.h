@@ -133,6 +133,7 @@ struct pfc_handle
   // lattice matrix-free path (pfc_lattice.cu): active when operator_kind = PFC_OPERATOR_MATRIX_FREE and the plan found
   // the uniform periodic tensor lattice
   bool lat = false;
+  bool q1_fast = true;          // Q1: closed-form kernels of pfc_ring_q1.cuh; off: PFC_Q1_CLOSED_FORM=0 / self-check
   bool lat_k_by_cells = false; // K product by the cell-quadrature kernel instead of the node stencil (self-check)
   pfc::LatGeom lat_geom;
 

@@ -9,6 +9,7 @@
 #include "pfc_handle.h"
 #include "pfc_lattice.cuh"
 #include "pfc_ring.cuh"
+#include "pfc_ring_q1.cuh"
 
 namespace pfc
 {
@@ -107,7 +108,16 @@ int lat_launch(pfc_handle *h, int mode, const LatOp &op, const Ctl *ctl)
     }
   switch (mode)
     {
-    case LAT_J: return q1 ? launch_mode<1, LAT_J>(h, op, ctl) : launch_mode<2, LAT_J>(h, op, ctl);
+    case LAT_J:
+      if (q1 && h->q1_fast)
+        { // closed-form Q1 algebra, constant blocks as stencils (pfc_ring_q1.cuh)
+          const LatGeom &G = h->lat_geom;
+          const dim3 grid((G.ncx + kCX - 2) / (kCX - 1), (G.ncy + kCY - 2) / (kCY - 1));
+          lat_j1_kernel<kCX, kCY><<<grid, kCX * kCY, 0, h->stream>>>(G, op, ctl);
+          h->launches++;
+          return PFC_OK;
+        }
+      return q1 ? launch_mode<1, LAT_J>(h, op, ctl) : launch_mode<2, LAT_J>(h, op, ctl);
     case LAT_S: return q1 ? launch_mode<1, LAT_S>(h, op, ctl) : launch_mode<2, LAT_S>(h, op, ctl);
     case LAT_K: return q1 ? launch_mode<1, LAT_K>(h, op, ctl) : launch_mode<2, LAT_K>(h, op, ctl);
     case LAT_R: return q1 ? launch_mode<1, LAT_R>(h, op, ctl) : launch_mode<2, LAT_R>(h, op, ctl);
@@ -176,9 +186,32 @@ static bool ring_deep(bool dflt)
   if (ring_deep(h->plan.degree == 1 ? DEEP1 : DEEP2))                                                           \
     return ring_launch<STAGES>(h, op, ctl, KERNEL<1, kRingThreads, 3>, KERNEL<2, kRingThreads, 5>);             \
   return ring_launch<STAGES>(h, op, ctl, KERNEL<1, kRingThreads, 1>, KERNEL<2, kRingThreads, 1>);
+// Q1: closed-form variants (pfc_ring_q1.cuh) unless switched off (self-check)
+#define PFC_RING_DISPATCH1(STAGES, KERNEL1, DEEP1)                                                              \
+  if (h->plan.degree == 1 && h->q1_fast)                                                                        \
+    {                                                                                                           \
+      if (ring_deep(DEEP1))                                                                                     \
+        return ring_launch<STAGES>(h, op, ctl, KERNEL1<kRingThreads, 3>, KERNEL1<kRingThreads, 3>);             \
+      return ring_launch<STAGES>(h, op, ctl, KERNEL1<kRingThreads, 1>, KERNEL1<kRingThreads, 1>);               \
+    }
 int ring_launch_t(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(1, ring_t_kernel, true, false) }
-int ring_launch_sweep(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(3, ring_sweep_kernel, true, false) }
-int ring_launch_back(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(2, ring_back_kernel, false, false) }
+int ring_launch_sweep(pfc_handle *h, const RingOp &op, const Ctl *ctl)
+{
+  PFC_RING_DISPATCH1(3, ring_sweep1_kernel, true)
+  PFC_RING_DISPATCH(3, ring_sweep_kernel, true, false)
+}
+int ring_launch_back(pfc_handle *h, const RingOp &op, const Ctl *ctl)
+{
+  PFC_RING_DISPATCH1(2, ring_back1_kernel, false)
+  PFC_RING_DISPATCH(2, ring_back_kernel, false, false)
+}
+int ring_launch_rhs1(pfc_handle *h, const RingOp &op, const Ctl *ctl)
+{
+  if (h->plan.degree != 1)
+    return h->fail(PFC_ERR_UNSUPPORTED, "ring_launch_rhs1 is a Q1 kernel");
+  return ring_launch<2>(h, op, ctl, ring_rhs1_kernel<kRingThreads>, ring_rhs1_kernel<kRingThreads>);
+}
+#undef PFC_RING_DISPATCH1
 #undef PFC_RING_DISPATCH
 
 // nodes N = w h; every field is read once (the halo ring through L2) and every output written once
@@ -195,6 +228,7 @@ double lat_bytes(const pfc_handle *h, int mode)
     case RING_T: return 32.0 * N;     // r1, r2 in, t, m1 out
     case RING_SWEEP: return 48.0 * N; // x, rhs, dinv, d in, d, x out
     case RING_BACK: return 40.0 * N;  // psi, r1, r2 in, chi, phi out
+    case RING_RHS1: return 64.0 * N;  // r0, r1, r2, psi, dinv in, rhs, d, x out (t kernel fused, Q1)
     case RING_RHS: return 72.0 * N;   // m1, t, psi, chi, r0, dinv in, rhs, d, x out
     default: return (h->prm.theta == 1.0 ? 32.0 : 48.0) * N + 32.0 * N; // state in, rhs + 1/diag(B) out
     }
@@ -267,6 +301,7 @@ int lat_setup(pfc_handle *h)
   const Ring &R = h->plan.ring; // padded rectangle of the ring overlay: every position has an arithmetic id
   cudaStream_t s = h->stream;
   LatGeom &G = h->lat_geom;
+  h->q1_fast = !(getenv("PFC_Q1_CLOSED_FORM") && atoi(getenv("PFC_Q1_CLOSED_FORM")) == 0); // tuning / A-B aid
   G.ncx = R.ncx;
   G.ncy = R.ncy;
   G.ex0 = R.ex0;

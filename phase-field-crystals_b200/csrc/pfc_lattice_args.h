@@ -29,7 +29,7 @@ enum
              // (stress_calculator_mpi.cpp:204-314)
   LAT_M = 5, // out[c zstride + r] = (M s0[c zstride + .])_r for the fields of zmask: consistent mass matrix as a
              // node stencil (stress_calculator_mpi.cpp:141-200)
-  RING_T = 6, RING_SWEEP = 7, RING_BACK = 8, RING_RHS = 9 // legs of the ring path (lat_bytes)
+  RING_T = 6, RING_SWEEP = 7, RING_BACK = 8, RING_RHS = 9, RING_RHS1 = 10 // legs of the ring path (lat_bytes)
 };
 
 struct LatOp
@@ -60,7 +60,12 @@ struct RingOp
   double *z;                 // back substitution: 3-component vector, x in component 0, writes chi, phi
   double bbar, dtth;
   int lo, rs, epi, out_vec, x_vec;
+  // Q1 fused right-hand side kernel (pfc_ring_q1.cuh)
+  const double *psi;         // state Psi_n (3-component vector): coefficient of C from its psi
+  double *out2;              // first Chebyshev iterate
+  double eps;
 };
+int ring_launch_rhs1(pfc_handle *h, const RingOp &op, const Ctl *ctl); // Q1 only
 int ring_launch_t(pfc_handle *h, const RingOp &op, const Ctl *ctl);
 int ring_launch_sweep(pfc_handle *h, const RingOp &op, const Ctl *ctl);
 int ring_launch_back(pfc_handle *h, const RingOp &op, const Ctl *ctl);

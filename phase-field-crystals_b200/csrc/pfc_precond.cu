@@ -222,32 +222,49 @@ static int precond_apply_ring(pfc_handle *h, double *in, double *out, const Ctl 
   const int p = P.degree, sw = h->sweeps;
   double *m1 = wv(h, W_M1), *t = wv(h, W_T), *rhs = wv(h, W_RHS), *xa = wv(h, W_XA), *xb = wv(h, W_XB), *d = wv(h, W_D);
   PFC_TRY(halo_exchange(h, in, ctl));
-  RingOp a;
-  std::memset(&a, 0, sizeof(a));
-  a.in = in;
-  a.t = t;
-  a.m1 = m1;
-  a.lo = p;
-  PFC_TRY(ring_launch_t(h, a, ctl));
-  {
-    LatOp op = lat_op(h); // rhs = r0 - C m1 - D t (exact, iterate-dependent C), d = x = dinv rhs / theta
-    op.in3b = h->d_psi_n.p;
-    op.s1 = m1;
-    op.s2 = t;
-    op.sB = 0.0;
-    op.sC = -1.0;
-    op.sD = -1.0;
-    op.add = in;
-    op.add_c = 0;
-    op.dinv = h->d_dinvB.p;
-    op.cheb = h->d_cheb.p;
-    op.d = d;
-    op.out = rhs;
-    op.out2 = xa;
-    op.epi = 0;
-    op.lo = 2 * p;
-    PFC_TRY(lat_launch(h, LAT_S, op, ctl));
-  }
+  if (p == 1 && h->q1_fast)
+    { // Q1: t kernel, Schur right-hand side and first Chebyshev step in one pass (pfc_ring_q1.cuh)
+      RingOp a;
+      std::memset(&a, 0, sizeof(a));
+      a.in = in;
+      a.psi = h->d_psi_n.p;
+      a.dinv = h->d_dinvB.p;
+      a.cheb = h->d_cheb.p;
+      a.d = d;
+      a.out = rhs;
+      a.out2 = xa;
+      a.dtth = h->prm.dt * h->prm.theta;
+      a.eps = h->prm.eps;
+      a.lo = 2 * p;
+      PFC_TRY(ring_launch_rhs1(h, a, ctl));
+    }
+  else
+    {
+      RingOp a;
+      std::memset(&a, 0, sizeof(a));
+      a.in = in;
+      a.t = t;
+      a.m1 = m1;
+      a.lo = p;
+      PFC_TRY(ring_launch_t(h, a, ctl));
+      LatOp op = lat_op(h); // rhs = r0 - C m1 - D t (exact, iterate-dependent C), d = x = dinv rhs / theta
+      op.in3b = h->d_psi_n.p;
+      op.s1 = m1;
+      op.s2 = t;
+      op.sB = 0.0;
+      op.sC = -1.0;
+      op.sD = -1.0;
+      op.add = in;
+      op.add_c = 0;
+      op.dinv = h->d_dinvB.p;
+      op.cheb = h->d_cheb.p;
+      op.d = d;
+      op.out = rhs;
+      op.out2 = xa;
+      op.epi = 0;
+      op.lo = 2 * p;
+      PFC_TRY(lat_launch(h, LAT_S, op, ctl));
+    }
   double *x = xa, *xn = xb;
   for (int i = 1; i < sw; ++i)
     {
@@ -356,6 +373,8 @@ extern "C" int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms5, double
   float ms;
   for (int leg = 0; leg < n_legs; ++leg)
     {
+      if (leg == 3 && h->lat && p == 1 && h->q1_fast)
+        continue; // Q1: the t kernel is fused into the right-hand side kernel (leg 2)
       cudaGraph_t graph = nullptr;
       cudaGraphExec_t exec = nullptr;
       const int64_t before = h->launches;
@@ -378,6 +397,12 @@ extern "C" int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms5, double
                   o.x = (i & 1) ? xn : x, o.out = (i & 1) ? x : xn, o.rhs = wv(h, W_RHS), o.dinv = h->d_dinvB.p;
                   o.cheb = h->d_cheb.p + 2, o.d = wv(h, W_D), o.lo = 5 * p;
                   rc = ring_launch_sweep(h, o, nullptr);
+                }
+              else if (leg == 2 && p == 1 && h->q1_fast)
+                {
+                  o.psi = h->d_psi_n.p, o.dinv = h->d_dinvB.p, o.cheb = h->d_cheb.p, o.d = wv(h, W_D), o.out = wv(h, W_RHS);
+                  o.out2 = x, o.eps = h->prm.eps, o.lo = 2 * p;
+                  rc = ring_launch_rhs1(h, o, nullptr);
                 }
               else if (leg == 2)
                 {
@@ -427,9 +452,80 @@ extern "C" int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms5, double
   if (bytes4)
     {
       bytes4[0] = h->lat ? lat_bytes(h, RING_SWEEP) : 12.0 * (double)P.n_ent + 32.0 * (double)P.Np;
-      bytes4[1] = h->lat ? lat_bytes(h, RING_RHS) : 36.0 * (double)P.n_ent + 64.0 * (double)P.Np;
-      bytes4[2] = h->lat ? lat_bytes(h, RING_T) : 0.0;
+      bytes4[1] = h->lat ? lat_bytes(h, (p == 1 && h->q1_fast) ? RING_RHS1 : RING_RHS) : 36.0 * (double)P.n_ent + 64.0 * (double)P.Np;
+      bytes4[2] = (h->lat && !(p == 1 && h->q1_fast)) ? lat_bytes(h, RING_T) : 0.0;
       bytes4[3] = h->lat ? lat_bytes(h, RING_BACK) : 0.0;
+    }
+  return PFC_OK;
+}
+
+// Q1 closed-form kernels (pfc_ring_q1.cuh) against the kernels they replace, on a pseudo-random vector tied to the global
+// node numbers: max_rel2[0] = J apply (lat_j1_kernel vs lat_kernel<1, LAT_J>), max_rel2[1] = preconditioner application
+// (fused right-hand side kernel, closed-form sweeps and back substitution vs t kernel + lat_kernel<1, LAT_S> + the
+// general ring kernels); max |a - b| / max |b| over the owned rows of all three components.  [collective]
+extern "C" int pfc_selfcheck_q1(pfc_handle *h, double *max_rel2)
+{
+  if (!h || !max_rel2)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->is_setup || !h->lat || h->plan.degree != 1 || !h->assembled || h->prm.preconditioner != PFC_PRECOND_BLOCK_SCHUR)
+    return h->fail(PFC_ERR_UNSUPPORTED, "pfc_selfcheck_q1 needs the Q1 lattice path, pfc_assemble and PFC_PRECOND_BLOCK_SCHUR");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  PFC_TRY(precond_refresh(h));
+  const Plan &P = h->plan;
+  const LatGeom &G = h->lat_geom;
+  const int64_t n = (int64_t)G.w * G.h, Np = P.Np;
+  cudaStream_t s = h->stream;
+  double *in = h->d_V.p, *ya = h->d_V.p + h->stride, *yb = h->d_V.p + 2 * h->stride;
+  std::vector<double> v((size_t)h->stride, 0.0), a((size_t)3 * Np), b((size_t)3 * Np);
+  for (int c = 0; c < 3; ++c)
+    for (int64_t r = 0; r < n; ++r)
+      {
+        uint64_t st = ((uint64_t)P.perm[r] * 3 + c) * 0x9E3779B97F4A7C15ull + 88172645463325252ull;
+        st ^= st << 13, st ^= st >> 7, st ^= st << 17;
+        v[c * Np + r] = (double)(st >> 11) / 9007199254740992.0 - 0.5;
+      }
+  const bool keep = h->q1_fast;
+  int rc = PFC_OK;
+  for (int leg = 0; leg < 2 && rc == PFC_OK; ++leg)
+    {
+      PFC_CUDA(h, cudaMemcpyAsync(in, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice, s));
+      PFC_CUDA(h, cudaMemsetAsync(ya, 0, h->stride * sizeof(double), s));
+      PFC_CUDA(h, cudaMemsetAsync(yb, 0, h->stride * sizeof(double), s));
+      for (int variant = 0; variant < 2 && rc == PFC_OK; ++variant)
+        {
+          h->q1_fast = variant == 0;
+          double *y = variant == 0 ? ya : yb;
+          if (leg == 0)
+            {
+              rc = halo_exchange(h, in, nullptr);
+              LatOp op = lat_op(h);
+              op.in3a = in;
+              op.in3b = h->d_psi_n.p;
+              op.out3 = y;
+              if (rc == PFC_OK)
+                rc = lat_launch(h, LAT_J, op, nullptr);
+            }
+          else
+            rc = precond_apply(h, in, y, nullptr);
+        }
+      h->q1_fast = keep;
+      if (rc != PFC_OK)
+        return rc;
+      PFC_CUDA(h, cudaGetLastError());
+      PFC_CUDA(h, cudaMemcpyAsync(a.data(), ya, a.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+      PFC_CUDA(h, cudaMemcpyAsync(b.data(), yb, b.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+      PFC_CUDA(h, cudaStreamSynchronize(s));
+      double worst = 0, scale = 0;
+      for (int c = 0; c < 3; ++c)
+        for (int64_t r = 0; r < n; ++r)
+          {
+            worst = std::max(worst, std::fabs(a[c * Np + r] - b[c * Np + r]));
+            scale = std::max(scale, std::fabs(b[c * Np + r]));
+          }
+      double e = scale > 0 ? worst / scale : 1.0; // an all-zero reference is a failure, too
+      if (!(e == e))
+        e = 1.0;
+      max_rel2[leg] = e;
     }
   return PFC_OK;
 }

@@ -473,6 +473,13 @@ def test_ring_smoother_and_selfchecks(built, degree, n_refines, sweeps):
     assert s.operator_info()[0] == built.OPERATOR_MATRIX_FREE
     assert s.selfcheck() <= 1e-12
     assert s.selfcheck_smoother() <= 1e-12
+    if degree == 1:
+        # closed-form Q1 kernels (csrc/pfc_ring_q1.cuh) against the general cell kernels, on a state with structure
+        s.set_state(Psi + 1e-2 * np.random.default_rng(3).standard_normal(Psi.size), Psi)
+        s.assemble()
+        ej, ep = s.selfcheck_q1()
+        print(f"Q1 closed-form kernels vs general: J apply {ej:.2e}, preconditioner {ep:.2e}")
+        assert ej <= 1e-12 and ep <= 1e-10
     if n_refines <= 6:
         s.set_state(Psi, Psi)
         g = s.step()
