@@ -110,10 +110,32 @@ int lat_launch(pfc_handle *h, int mode, const LatOp &op, const Ctl *ctl)
     {
     case LAT_J:
       if (q1 && h->q1_fast)
-        { // closed-form Q1 algebra, constant blocks as stencils (pfc_ring_q1.cuh)
+        { // closed-form Q1 algebra, constant blocks as stencils, cp.async pipeline over a tile row (pfc_ring_q1.cuh)
+          static const int variant = getenv("PFC_J1_VARIANT") ? atoi(getenv("PFC_J1_VARIANT")) : 6; // tuning aid
           const LatGeom &G = h->lat_geom;
-          const dim3 grid((G.ncx + kCX - 2) / (kCX - 1), (G.ncy + kCY - 2) / (kCY - 1));
-          lat_j1_kernel<kCX, kCY><<<grid, kCX * kCY, 0, h->stream>>>(G, op, ctl);
+#define PFC_J1(CX, CY, NTILE, MINB)                                                                               \
+  {                                                                                                           \
+    const int ntx = (G.ncx + CX - 2) / (CX - 1), nty = (G.ncy + CY - 2) / (CY - 1);                           \
+    lat_j1_kernel<CX, CY, NTILE, MINB><<<dim3((ntx + NTILE - 1) / NTILE, nty), CX * CY, 0, h->stream>>>(G, op, ctl); \
+  }
+          switch (variant)
+            {
+            case 0: PFC_J1(16, 16, 1, 4) break;
+            case 2: PFC_J1(16, 16, 8, 2) break;
+            case 3: PFC_J1(32, 8, 4, 3) break;
+            case 4: PFC_J1(16, 8, 1, 8) break;
+            case 5: PFC_J1(16, 8, 8, 6) break;
+            case 7: PFC_J1(16, 16, 4, 4) break;
+            case 8: PFC_J1(16, 16, 4, 2) break;
+            case 1: PFC_J1(16, 16, 4, 3) break;
+            case 9: PFC_J1(64, 4, 4, 3) break;
+            case 10: PFC_J1(32, 4, 16, 6) break;
+            case 11: PFC_J1(32, 4, 4, 6) break;
+            case 12: PFC_J1(32, 8, 8, 3) break;
+            case 13: PFC_J1(64, 4, 8, 3) break;
+            default: PFC_J1(32, 4, 8, 6) break; // measured best on B200 (profiles/r02k_j1_tuning.log)
+            }
+#undef PFC_J1
           h->launches++;
           return PFC_OK;
         }

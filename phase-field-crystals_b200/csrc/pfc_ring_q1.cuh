@@ -417,141 +417,169 @@ static __global__ void __launch_bounds__(NT) ring_back1_kernel(LatGeom L, RingOp
     ring_back1_rows<NT, PF, false>(L, O, s_ex, X0 + tid, Y0, Y1);
 }
 
-// ---- J apply on a tile of cells (Q1) --------------------------------------------------------------------------------
-// y = J z on the owned nodes.  Same tiling as lat_kernel<1, LAT_J> (one thread per cell, the nodes of the inner
-// (CX-1) x (CY-1) cells are the CTA's own), but only B z_psi + C z_chi goes through the Gauss points (q1:: algebra);
+// ---- J apply on tiles of cells (Q1) ---------------------------------------------------------------------------------
+// y = J z on the owned nodes.  Tiling as lat_kernel<1, LAT_J> (one thread per cell, the nodes of the inner
+// (CX-1) x (CY-1) cells are the tile's own), but only B z_psi + C z_chi goes through the Gauss points (q1:: algebra);
 // K z_psi + M z_chi, K z_chi + M z_phi and D z_phi are 9-point stencils on the staged nodal values.
-template <int CX, int CY>
-static __global__ void __launch_bounds__(CX *CY) lat_j1_kernel(LatGeom L, LatOp O, const Ctl *ctl)
+// With half the arithmetic of the general kernel the load latency of a tile is no longer hidden by the arithmetic of
+// the other resident CTAs (measured: 522 -> 510 us), so a CTA walks over NTILE tiles of a tile row and stages the
+// nodal values of the next tile with cp.async (LDGSTS, 8 bytes: a tile row starts at any node) while it works on the
+// current one; two shared-memory buffers.  NTILE = 1: plain version, no pipeline.
+__device__ __forceinline__ void cp_async8(double *smem_dst, const double *gsrc)
+{
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait()
+{
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
+template <int CX, int CY, int NTILE, int MINB>
+static __global__ void __launch_bounds__(CX *CY, MINB) lat_j1_kernel(LatGeom L, LatOp O, const Ctl *ctl)
 {
   if (ctl && ctl->state != 0)
     return;
-  constexpr int NT = CX * CY, NF = 5, TNX = CX + 1, TNY = CY + 1, TN = TNX * TNY;
-  __shared__ double s_in[NF][TN]; // z_psi, z_chi, z_phi, psi_n, chi_n
-  __shared__ double s_c[4][NT];   // corner contributions [iy * 2 + ix] of every cell
+  constexpr int NT = CX * CY, NF = 5, TNX = CX + 1, TNY = CY + 1, TN = TNX * TNY, NBUF = NTILE > 1 ? 2 : 1;
+  constexpr int ITER = (TN + NT - 1) / NT, ONX = CX - 1, ONY = CY - 1;
+  __shared__ double s_in[NBUF][NF][TN]; // z_psi, z_chi, z_phi, psi_n, chi_n
+  __shared__ double s_c[4][NT];         // corner contributions [iy * 2 + ix] of every cell
   const int tid = threadIdx.x;
-  const int ax0 = blockIdx.x * (CX - 1), ay0 = blockIdx.y * (CY - 1); // first inner cell of the tile
-  const int nx0 = ax0 - 1, ny0 = ay0 - 1;                             // padded position of tile node (0, 0)
+  const int ntx = (L.ncx + CX - 2) / (CX - 1);
+  const int bx0 = blockIdx.x * NTILE, nt = min(NTILE, ntx - bx0);
+  const int ay0 = blockIdx.y * (CY - 1), ny0 = ay0 - 1; // first inner cell row of the tile row; padded row of tile node row 0
   const int64_t Np = L.Np;
-  // tiles whose nodes all lie in the owned rectangle address by arithmetic (nearly all of them)
-  const bool fast = nx0 >= L.ex0 && nx0 + TNX <= L.ex0 + L.w && ny0 >= L.ey0 && ny0 + TNY <= L.ey0 + L.h;
-  {
-    constexpr int ITER = (TN + NT - 1) / NT;
-    double f[ITER][NF];
+  const double dtth = O.dt * O.theta;
+  const bool rows_owned = ny0 >= L.ey0 && ny0 + TNY <= L.ey0 + L.h;
+
+  // stage the nodal values of tile bx into buffer buf (asynchronously; zeros outside the padded rectangle)
+  auto stage = [&](int buf, int bx) {
+    const int nx0 = bx * (CX - 1) - 1;
+    const bool fast = rows_owned && nx0 >= L.ex0 && nx0 + TNX <= L.ex0 + L.w; // all nodes owned: arithmetic ids
 #pragma unroll
     for (int it = 0; it < ITER; ++it)
       {
         const int idx = tid + it * NT;
+        if (idx >= TN)
+          break;
         const int ex = nx0 + idx % TNX, ey = ny0 + idx / TNX;
-#pragma unroll
-        for (int k = 0; k < NF; ++k)
-          f[it][k] = 0;
         if (fast)
           {
-            if (idx < TN)
-              {
-                const int64_t u = (int64_t)(ey - L.ey0) * L.w + (ex - L.ex0);
-                f[it][0] = O.in3a[u];
-                f[it][1] = O.in3a[Np + u];
-                f[it][2] = O.in3a[2 * Np + u];
-                f[it][3] = O.in3b[u];
-                f[it][4] = O.in3b[Np + u];
-              }
+            const int64_t u = (int64_t)(ey - L.ey0) * L.w + (ex - L.ex0);
+            cp_async8(&s_in[buf][0][idx], O.in3a + u);
+            cp_async8(&s_in[buf][1][idx], O.in3a + Np + u);
+            cp_async8(&s_in[buf][2][idx], O.in3a + 2 * Np + u);
+            cp_async8(&s_in[buf][3][idx], O.in3b + u);
+            cp_async8(&s_in[buf][4][idx], O.in3b + Np + u);
           }
-        else if (idx < TN && ex >= 0 && ex < L.fw && ey >= 0 && ey < L.fh)
+        else if (ex >= 0 && ex < L.fw && ey >= 0 && ey < L.fh)
           {
             const int32_t u = lat_id(L, ex, ey);
-            f[it][0] = O.in3a[vaddr(u, 0, Np)];
-            f[it][1] = O.in3a[vaddr(u, 1, Np)];
-            f[it][2] = O.in3a[vaddr(u, 2, Np)];
-            f[it][3] = O.in3b[vaddr(u, 0, Np)];
-            f[it][4] = O.in3b[vaddr(u, 1, Np)];
+            cp_async8(&s_in[buf][0][idx], O.in3a + vaddr(u, 0, Np));
+            cp_async8(&s_in[buf][1][idx], O.in3a + vaddr(u, 1, Np));
+            cp_async8(&s_in[buf][2][idx], O.in3a + vaddr(u, 2, Np));
+            cp_async8(&s_in[buf][3][idx], O.in3b + vaddr(u, 0, Np));
+            cp_async8(&s_in[buf][4][idx], O.in3b + vaddr(u, 1, Np));
           }
-      }
-#pragma unroll
-    for (int it = 0; it < ITER; ++it)
-      {
-        const int idx = tid + it * NT;
-        if (idx < TN)
+        else
           {
 #pragma unroll
             for (int k = 0; k < NF; ++k)
-              s_in[k][idx] = f[it][k];
+              s_in[buf][k][idx] = 0.0;
           }
       }
-  }
-  __syncthreads();
-  const double dtth = O.dt * O.theta;
-  { // ---- one cell per thread: B z_psi + C z_chi at the 2 x 2 Gauss points (mpi.cpp:421-433) ----
-    const int cx = tid % CX, cy = tid / CX;
-    const int kx = ax0 - 1 + cx, ky = ay0 - 1 + cy;
-    const bool cell_ok = kx >= 0 && kx < L.ncx && ky >= 0 && ky < L.ncy;
-    const int o = cy * TNX + cx;
-    auto xs = [&](int fld, int row) { return q1::xstage(s_in[fld][o + row * TNX], s_in[fld][o + row * TNX + 1]); };
-    double psi[2][2], chi[2][2], v0[2][2], v1[2][2], pdy[2], pdx[2], zdy[2], zdx[2], tmp[2];
+    cp_async_commit();
+  };
+
+  stage(0, bx0);
+  for (int k = 0; k < nt; ++k)
     {
-      const q1::XS t = xs(3, 0), b = xs(3, 1);
-      q1::values(t, b, psi, pdy);
-      q1::xderiv(t, b, pdx);
-    }
-    q1::values(xs(4, 0), xs(4, 1), chi, tmp);
-    {
-      const q1::XS t = xs(0, 0), b = xs(0, 1);
-      q1::values(t, b, v0, zdy);
-      q1::xderiv(t, b, zdx);
-    }
-    q1::values(xs(1, 0), xs(1, 1), v1, tmp);
-    // physical gradients: d/dx at Gauss row qy = dx[qy] / hx, d/dy at Gauss column qx = dy[qx] / hy
-    const double ihx2 = L.ihx * L.ihx, ihy2 = L.ihy * L.ihy;
-    const double cm0 = -dtth * (1.0 + O.eps);
-    double A[2][2], c[2][2];
-#pragma unroll
-    for (int qy = 0; qy < 2; ++qy)
-#pragma unroll
-      for (int qx = 0; qx < 2; ++qx)
+      const int buf = NBUF == 2 ? (k & 1) : 0;
+      if (NBUF == 2 && k + 1 < nt)
         {
-          const double p = psi[qy][qx];
-          const double g2 = fma(pdx[qy] * pdx[qy], ihx2, pdy[qx] * pdy[qx] * ihy2); // |grad psi|^2
-          const double gz = fma(pdx[qy] * zdx[qy], ihx2, pdy[qx] * zdy[qx] * ihy2); // grad psi . grad z_psi
-          const double bm = fma(-6.0 * dtth, fma(p, chi[qy][qx], g2), 1.0);
-          const double cm = fma(-3.0 * dtth * p, p, cm0);
-          A[qy][qx] = fma(bm, v0[qy][qx], fma(-12.0 * dtth * p, gz, cm * v1[qy][qx]));
+          stage(buf ^ 1, bx0 + k + 1);
+          cp_async_wait<1>();
         }
-    q1::test(A, c);
-    s_c[0][tid] = cell_ok ? c[0][0] : 0.0;
-    s_c[1][tid] = cell_ok ? c[0][1] : 0.0;
-    s_c[2][tid] = cell_ok ? c[1][0] : 0.0;
-    s_c[3][tid] = cell_ok ? c[1][1] : 0.0;
-  }
-  __syncthreads();
-  // ---- nodes of the inner cells: the four corner contributions in a fixed order + the constant 9-point stencils ----
-  constexpr int ONX = CX - 1, ONY = CY - 1;
-  if (tid >= ONX * ONY)
-    return;
-  const int i = 1 + tid % ONX, j = 1 + tid / ONX; // tile node
-  if (!fast && !lat_in_window(L, -1, nx0 + i, ny0 + j))
-    return;
-  const double var = (s_c[3][(j - 1) * CX + i - 1] + s_c[2][(j - 1) * CX + i]) + (s_c[1][j * CX + i - 1] + s_c[0][j * CX + i]);
-  const q1::Cst C(L);
-  double K0, K1, K2, M1, M2, Mnone;
-  {
-    double wk[3], wm[3];
+      else
+        cp_async_wait<0>();
+      __syncthreads();
+      const int ax0 = (bx0 + k) * (CX - 1), nx0 = ax0 - 1;
+      const double(*S)[TN] = s_in[buf];
+      { // ---- one cell per thread: B z_psi + C z_chi at the 2 x 2 Gauss points (mpi.cpp:421-433) ----
+        const int cx = tid % CX, cy = tid / CX;
+        const int kx = ax0 - 1 + cx, ky = ay0 - 1 + cy;
+        const bool cell_ok = kx >= 0 && kx < L.ncx && ky >= 0 && ky < L.ncy;
+        const int o = cy * TNX + cx;
+        auto xs = [&](int fld, int row) { return q1::xstage(S[fld][o + row * TNX], S[fld][o + row * TNX + 1]); };
+        double psi[2][2], chi[2][2], v0[2][2], v1[2][2], pdy[2], pdx[2], zdy[2], zdx[2], tmp[2];
+        {
+          const q1::XS t = xs(3, 0), b = xs(3, 1);
+          q1::values(t, b, psi, pdy);
+          q1::xderiv(t, b, pdx);
+        }
+        q1::values(xs(4, 0), xs(4, 1), chi, tmp);
+        {
+          const q1::XS t = xs(0, 0), b = xs(0, 1);
+          q1::values(t, b, v0, zdy);
+          q1::xderiv(t, b, zdx);
+        }
+        q1::values(xs(1, 0), xs(1, 1), v1, tmp);
+        // physical gradients: d/dx at Gauss row qy = dx[qy] / hx, d/dy at Gauss column qx = dy[qx] / hy
+        const double ihx2 = L.ihx * L.ihx, ihy2 = L.ihy * L.ihy;
+        const double cm0 = -dtth * (1.0 + O.eps);
+        double A[2][2], c[2][2];
 #pragma unroll
-    for (int r = 0; r < 3; ++r)
-      q1::xsum(&s_in[0][(j - 1 + r) * TNX + i - 1], wk[r], wm[r]);
-    q1::ysum<false>(C, 2, wk, wm, K0, Mnone); // phase 2: slots (0, 1, 2) = (oldest, centre, newest)
+        for (int qy = 0; qy < 2; ++qy)
 #pragma unroll
-    for (int r = 0; r < 3; ++r)
-      q1::xsum(&s_in[1][(j - 1 + r) * TNX + i - 1], wk[r], wm[r]);
-    q1::ysum<true>(C, 2, wk, wm, K1, M1);
+          for (int qx = 0; qx < 2; ++qx)
+            {
+              const double p = psi[qy][qx];
+              const double g2 = fma(pdx[qy] * pdx[qy], ihx2, pdy[qx] * pdy[qx] * ihy2); // |grad psi|^2
+              const double gz = fma(pdx[qy] * zdx[qy], ihx2, pdy[qx] * zdy[qx] * ihy2); // grad psi . grad z_psi
+              const double bm = fma(-6.0 * dtth, fma(p, chi[qy][qx], g2), 1.0);
+              const double cm = fma(-3.0 * dtth * p, p, cm0);
+              A[qy][qx] = fma(bm, v0[qy][qx], fma(-12.0 * dtth * p, gz, cm * v1[qy][qx]));
+            }
+        q1::test(A, c);
+        s_c[0][tid] = cell_ok ? c[0][0] : 0.0;
+        s_c[1][tid] = cell_ok ? c[0][1] : 0.0;
+        s_c[2][tid] = cell_ok ? c[1][0] : 0.0;
+        s_c[3][tid] = cell_ok ? c[1][1] : 0.0;
+      }
+      __syncthreads();
+      // ---- nodes of the inner cells: the four corner contributions in a fixed order + the constant 9-point stencils ----
+      if (tid < ONX * ONY)
+        {
+          const int i = 1 + tid % ONX, j = 1 + tid / ONX; // tile node
+          if (lat_in_window(L, -1, nx0 + i, ny0 + j))
+            {
+              const double var =
+                (s_c[3][(j - 1) * CX + i - 1] + s_c[2][(j - 1) * CX + i]) + (s_c[1][j * CX + i - 1] + s_c[0][j * CX + i]);
+              const q1::Cst C(L);
+              double K0, K1, K2, M1, M2, Mnone;
+              double wk[3], wm[3];
 #pragma unroll
-    for (int r = 0; r < 3; ++r)
-      q1::xsum(&s_in[2][(j - 1 + r) * TNX + i - 1], wk[r], wm[r]);
-    q1::ysum<true>(C, 2, wk, wm, K2, M2);
-  }
-  const int64_t r = (int64_t)(ny0 + j - L.ey0) * L.w + (nx0 + i - L.ex0); // owned: ly w + lx
-  O.out3[r] = fma(0.25 * L.hx * L.hy, var, dtth * fma(-2.0, M2, K2));
-  O.out3[Np + r] = K0 + M1;
-  O.out3[2 * Np + r] = K1 + M2;
+              for (int r = 0; r < 3; ++r)
+                q1::xsum(&S[0][(j - 1 + r) * TNX + i - 1], wk[r], wm[r]);
+              q1::ysum<false>(C, 2, wk, wm, K0, Mnone); // phase 2: slots (0, 1, 2) = (oldest, centre, newest)
+#pragma unroll
+              for (int r = 0; r < 3; ++r)
+                q1::xsum(&S[1][(j - 1 + r) * TNX + i - 1], wk[r], wm[r]);
+              q1::ysum<true>(C, 2, wk, wm, K1, M1);
+#pragma unroll
+              for (int r = 0; r < 3; ++r)
+                q1::xsum(&S[2][(j - 1 + r) * TNX + i - 1], wk[r], wm[r]);
+              q1::ysum<true>(C, 2, wk, wm, K2, M2);
+              const int64_t r = (int64_t)(ny0 + j - L.ey0) * L.w + (nx0 + i - L.ex0); // owned: ly w + lx
+              O.out3[r] = fma(0.25 * L.hx * L.hy, var, dtth * fma(-2.0, M2, K2));
+              O.out3[Np + r] = K0 + M1;
+              O.out3[2 * Np + r] = K1 + M2;
+            }
+        }
+      if (k + 1 < nt)
+        __syncthreads(); // s_c and this buffer are rewritten by the next round
+    }
 }
 } // namespace pfc
