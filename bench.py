@@ -272,16 +272,22 @@ def kernel_legs(solver, stats, sweeps, precond, mf, peak, n_nodes, ms_per_step):
                       "launches_per_step": per_step, "share_of_step": ms * per_step / ms_per_step}
 
     ms_op, by_op = solver.time_operator(reps=20)
-    add("J apply: lat_kernel<LAT_J>" if mf else "J apply: spmv_sell_kernel", ms_op, by_op, n_it + n_solve)
+    add(("J apply: lat_j1_kernel" if solver.params.degree == 1 else "J apply: lat_kernel<LAT_J>") if mf else "J apply: spmv_sell_kernel",
+        ms_op, by_op, n_it + n_solve)
     if precond:
         pc = solver.time_precond(reps=20)
         n_pc = n_it + n_solve  # one application per iteration + the x update at the end of a cycle
         ms, by = pc["ms"], pc["bytes"]
         if mf:
-            add("Chebyshev sweep on the Schur complement: ring_sweep_kernel", ms[1], by[0], n_pc * (sweeps - 1))
-            add("Schur right-hand side + first Chebyshev step: lat_kernel<LAT_S>", ms[2], by[1], n_pc)
-            add("t = M_L^-1 (r2 - K M_L^-1 r1): ring_t_kernel", ms[3], by[2], n_pc)
-            add("back substitution chi, phi: ring_back_kernel", ms[4], by[3], n_pc)
+            q1 = ms[3] == 0.0  # Q1: closed-form kernels (csrc/pfc_ring_q1.cuh), the t kernel is fused into the right-hand side
+            add("Chebyshev sweep on the Schur complement: " + ("ring_sweep1_kernel" if q1 else "ring_sweep_kernel"), ms[1], by[0],
+                n_pc * (sweeps - 1))
+            if q1:
+                add("t kernel + Schur right-hand side + first Chebyshev step: ring_rhs1_kernel", ms[2], by[1], n_pc)
+            else:
+                add("Schur right-hand side + first Chebyshev step: lat_kernel<LAT_S>", ms[2], by[1], n_pc)
+                add("t = M_L^-1 (r2 - K M_L^-1 r1): ring_t_kernel", ms[3], by[2], n_pc)
+            add("back substitution chi, phi: " + ("ring_back1_kernel" if q1 else "ring_back_kernel"), ms[4], by[3], n_pc)
         else:
             add("K product: kmv_kernel", ms[1], by[0], n_pc * (2 * sweeps + 1))
             add("Schur row: bcd_kernel", ms[2], by[1], n_pc * sweeps)
@@ -522,7 +528,7 @@ def main():
     # ---- roofline legs on resident data (rank-local kernels) ----
     peak, peak_src = measured_peak()
     ms_per_step = ms_dev / args.steps
-    sweeps = args.sweeps if args.sweeps > 0 else (5 if degree == 2 else 3)
+    sweeps = args.sweeps if args.sweeps > 0 else (5 if degree == 2 else (4 if args.mf else 3))  # the library's defaults
     legs = None
     if not args.no_legs:
         solver.assemble()

@@ -96,7 +96,10 @@ extern "C" int pfc_create(const pfc_params *p, pfc_handle **out)
   h->restart = ntmp - 2;
   h->n_basis = ntmp - 1;
   // Chebyshev degree: measured optimum of the lattice path on M2-sized meshes (profiles/README.md): Q2 5, Q1 3
-  h->sweeps = p->precond_sweeps > 0 ? p->precond_sweeps : (p->degree == 2 ? 5 : 3);
+  // default Chebyshev degree: measured best per path (M2: 5; M4 matrix-free with the cheap streaming sweeps: 4, 226 against
+  // 237 ms per step at 3 or 5, profiles/r02r)
+  h->sweeps = p->precond_sweeps > 0 ? p->precond_sweeps
+                                    : (p->degree == 2 ? 5 : (p->operator_kind == PFC_OPERATOR_MATRIX_FREE ? 4 : 3));
   int dev = p->device;
   if (dev < 0)
     cudaGetDevice(&dev);
@@ -275,6 +278,8 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
       }
   }
   h->stride = (P.Lv + 15) / 16 * 16;
+  if (const char *e = getenv("PFC_STRIDE_PAD")) // tuning aid: distance between the Krylov basis vectors, see profiles/stride_sweep.sh
+    h->stride += std::max(0, atoi(e)) / 16 * 16;
   const size_t ne = (size_t)P.n_ent;
   PFC_CUDA(h, h->d_B.alloc(ne));
   PFC_CUDA(h, h->d_C.alloc(ne));

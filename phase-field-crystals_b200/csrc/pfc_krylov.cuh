@@ -78,11 +78,14 @@ __device__ __forceinline__ void grid_reduce(double (&acc)[NV], double *partial, 
 
 // out[i] = V_i . w for i < DIM, out[DIM] = w . w        (one pass over DIM + 1 vectors)
 // pass 1 (second Gram-Schmidt pass) runs only if ctl->reorth is set.
+// Loads are issued in batches of kGsBatch vectors before their products: under register pressure (DIM >= 21) ptxas
+// otherwise alternates one load with one product, and a thread then has two loads in flight instead of eight
+// (measured 3.7 instead of 6.7 TB/s at DIM 24).  DIM >= 12 asks for two CTAs per SM (128 registers).
+constexpr int kGsBatch = 8;
 template <int DIM>
-static __global__ void __launch_bounds__(kVecThreads) multidot_kernel(const double *__restrict__ V, int64_t stride,
-                                                               const double *__restrict__ w, int64_t n2,
-                                                               double *partial, double *out,
-                                                               unsigned int *counter, const Ctl *ctl, int pass, ArDev ar)
+static __global__ void __launch_bounds__(kVecThreads, DIM >= 12 ? 2 : 3)
+  multidot_kernel(const double *__restrict__ V, int64_t stride, const double *__restrict__ w, int64_t n2, double *partial,
+                  double *out, unsigned int *counter, const Ctl *ctl, int pass, ArDev ar)
 {
   (void)pass;
   if (ctl && ctl->state != 0)
@@ -97,10 +100,17 @@ static __global__ void __launch_bounds__(kVecThreads) multidot_kernel(const doub
       const double2 wv = w2[idx];
       acc[DIM] += wv.x * wv.x + wv.y * wv.y;
 #pragma unroll
-      for (int i = 0; i < DIM; ++i)
+      for (int i0 = 0; i0 < DIM; i0 += kGsBatch)
         {
-          const double2 v = __ldg(reinterpret_cast<const double2 *>(V + (int64_t)i * stride) + idx);
-          acc[i] += v.x * wv.x + v.y * wv.y;
+          double2 v[kGsBatch];
+#pragma unroll
+          for (int b = 0; b < kGsBatch; ++b)
+            if (i0 + b < DIM)
+              v[b] = __ldg(reinterpret_cast<const double2 *>(V + (int64_t)(i0 + b) * stride) + idx);
+#pragma unroll
+          for (int b = 0; b < kGsBatch; ++b)
+            if (i0 + b < DIM)
+              acc[i0 + b] += v[b].x * wv.x + v[b].y * wv.y;
         }
     }
   grid_reduce<DIM + 1>(acc, partial, out, counter, ar);
@@ -109,11 +119,10 @@ static __global__ void __launch_bounds__(kVecThreads) multidot_kernel(const doub
 // w -= sum_i h_i V_i ; out[0] = ||w||^2 after the update.  The last block also applies the
 // Kelley test (pass 0): if ||w'|| <= 10 sqrt(eps) ||w|| the sticky reorth flag is raised.
 template <int DIM>
-static __global__ void __launch_bounds__(kVecThreads) multiaxpy_kernel(const double *__restrict__ V, int64_t stride,
-                                                                double *__restrict__ w, int64_t n2,
-                                                                const double *__restrict__ h, double *partial,
-                                                                double *out, unsigned int *counter, Ctl *ctl,
-                                                                int pass, ArDev ar)
+static __global__ void __launch_bounds__(kVecThreads, DIM >= 12 ? 2 : 3)
+  multiaxpy_kernel(const double *__restrict__ V, int64_t stride, double *__restrict__ w, int64_t n2,
+                   const double *__restrict__ h, double *partial, double *out, unsigned int *counter, Ctl *ctl, int pass,
+                   ArDev ar)
 {
   (void)pass;
   if (ctl->state != 0)
@@ -128,11 +137,20 @@ static __global__ void __launch_bounds__(kVecThreads) multiaxpy_kernel(const dou
     {
       double2 wv = w2[idx];
 #pragma unroll
-      for (int i = 0; i < DIM; ++i)
+      for (int i0 = 0; i0 < DIM; i0 += kGsBatch)
         {
-          const double2 v = __ldg(reinterpret_cast<const double2 *>(V + (int64_t)i * stride) + idx);
-          wv.x -= hh[i] * v.x;
-          wv.y -= hh[i] * v.y;
+          double2 v[kGsBatch];
+#pragma unroll
+          for (int b = 0; b < kGsBatch; ++b)
+            if (i0 + b < DIM)
+              v[b] = __ldg(reinterpret_cast<const double2 *>(V + (int64_t)(i0 + b) * stride) + idx);
+#pragma unroll
+          for (int b = 0; b < kGsBatch; ++b)
+            if (i0 + b < DIM)
+              {
+                wv.x -= hh[i0 + b] * v[b].x;
+                wv.y -= hh[i0 + b] * v[b].y;
+              }
         }
       w2[idx] = wv;
       acc[0] += wv.x * wv.x + wv.y * wv.y;

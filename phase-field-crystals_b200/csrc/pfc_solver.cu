@@ -203,14 +203,35 @@ struct Tab<0>
 };
 static DotFn g_dot[kMaxDim + 1];
 static AxpyFn g_axpy[kMaxDim + 1];
+static int g_dot_occ[kMaxDim + 1], g_axpy_occ[kMaxDim + 1]; // resident CTAs per SM of every instantiation
 static bool g_tab_ready = false;
 static void ensure_tab()
 {
   if (!g_tab_ready)
     {
       Tab<kMaxDim>::fill(g_dot, g_axpy);
+      for (int d = 0; d <= kMaxDim; ++d)
+        {
+          int nd = 0, na = 0;
+          if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nd, g_dot[d], kVecThreads, 0) != cudaSuccess || nd < 1)
+            nd = 1;
+          if (!g_axpy[d] || cudaOccupancyMaxActiveBlocksPerMultiprocessor(&na, g_axpy[d], kVecThreads, 0) != cudaSuccess || na < 1)
+            na = 1;
+          g_dot_occ[d] = nd;
+          g_axpy_occ[d] = na;
+        }
+      cudaGetLastError();
       g_tab_ready = true;
     }
+}
+// The Gram-Schmidt kernels are persistent grid-stride loops: exactly one wave of CTAs.  Their register count, and with
+// it the CTAs an SM holds, changes with the Krylov dimension (2 to 8); a grid of 4 per SM left a quarter of the vector
+// to a second wave of one CTA per SM at the dimensions that fit only 3 (measured: 2.7 instead of 6.7 TB/s at dimension 24,
+// profiles/r02o_krylov_dims.log).
+static inline int gs_grid(const pfc_handle *h, int64_t n2, int occ)
+{
+  const int64_t need = (n2 + kVecThreads - 1) / kVecThreads;
+  return (int)std::max<int64_t>(1, std::min<int64_t>(need, std::min<int64_t>((int64_t)h->n_sm * occ, 4096)));
 }
 
 // ---- one restart cycle, or the piece [i0, i1) of its iterations, enqueued on the stream (captured into a CUDA
@@ -260,18 +281,18 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0,
         }
       else
         PFC_TRY(apply_operator(h, V + (int64_t)inner * st, w, ctl)); // A.vmult
-      g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots0, cnt, ctl, 0, ar);
+      g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots0, cnt, ctl, 0, ar);
       if (!fused)
         PFC_TRY(allreduce_sum(h, g->dots0, dim + 1, ctl));
-      g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots0, partial, &g->nrm2[0], cnt, ctl, 0, ar);
+      g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, st, w, n2, g->dots0, partial, &g->nrm2[0], cnt, ctl, 0, ar);
       if (!fused)
         PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1, ctl));
       if (two_pass)
         {
-          g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots1, cnt, ctl, 1, ar);
+          g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots1, cnt, ctl, 1, ar);
           if (!fused)
             PFC_TRY(allreduce_sum(h, g->dots1, dim + 1, ctl));
-          g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, st, w, n2, g->dots1, partial, &g->nrm2[1], cnt, ctl, 1, ar);
+          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, st, w, n2, g->dots1, partial, &g->nrm2[1], cnt, ctl, 1, ar);
           if (!fused)
             PFC_TRY(allreduce_sum(h, &g->nrm2[1], 1, ctl));
           h->launches += 2;
@@ -663,15 +684,15 @@ extern "C" int pfc_time_krylov(pfc_handle *h, int32_t dim, int32_t reps, double 
     {
       for (int i = 0; i < 2; ++i) // warm-up
         if (k == 0)
-          g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0, ArDev{});
+          g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0, ArDev{});
         else
-          g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
+          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
       PFC_CUDA(h, cudaEventRecord(h->ev[0], s));
       for (int i = 0; i < reps; ++i)
         if (k == 0)
-          g_dot[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0, ArDev{});
+          g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0, ArDev{});
         else
-          g_axpy[dim]<<<grid, kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
+          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
       h->launches += reps + 2;
       PFC_CUDA(h, cudaEventRecord(h->ev[1], s));
       PFC_CUDA(h, cudaStreamSynchronize(s));
