@@ -261,25 +261,8 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
           map[P.block_start[c] + P.ghost_global[g]] = 3 * (P.Np + g) + c;
     PFC_CUDA(h, h->d_api_map.upload(map, s));
     PFC_CUDA(h, cudaStreamSynchronize(s));
-    // reading only: a slave of another rank on this rank's cells reads its master (the old ghost list carried such
-    // slaves; the ring carries the node a position resolves to).  A second map, only where such slaves exist.
-    h->d_api_gather.release();
-    int64_t aliases = 0;
-    for (int64_t k = 0; k < mesh->n_constraints; ++k)
-      {
-        const int64_t sl = mesh->constraint_slave[k], ms = mesh->constraint_master[k];
-        if (sl >= 0 && sl < P.n_dofs && ms >= 0 && ms < P.n_dofs && map[sl] < 0 && map[ms] >= 0)
-          map[sl] = map[ms], ++aliases;
-      }
-    if (aliases > 0)
-      {
-        PFC_CUDA(h, h->d_api_gather.upload(map, s));
-        PFC_CUDA(h, cudaStreamSynchronize(s));
-      }
   }
   h->stride = (P.Lv + 15) / 16 * 16;
-  if (const char *e = getenv("PFC_STRIDE_PAD")) // tuning aid: distance between the Krylov basis vectors, see profiles/stride_sweep.sh
-    h->stride += std::max(0, atoi(e)) / 16 * 16;
   const size_t ne = (size_t)P.n_ent;
   PFC_CUDA(h, h->d_B.alloc(ne));
   PFC_CUDA(h, h->d_C.alloc(ne));
@@ -483,7 +466,7 @@ static int download_vector(pfc_handle *h, const double *dvec, double *host)
   const int64_t n = h->plan.n_dofs;
   const int blocks = (int)((n + 255) / 256);
   PFC_CUDA(h, cudaMemsetAsync(h->d_io.p, 0, n * sizeof(double), h->stream));
-  gather_kernel<<<blocks, 256, 0, h->stream>>>(h->d_io.p, dvec, h->d_api_gather.p ? h->d_api_gather.p : h->d_api_map.p, n,
+  gather_kernel<<<blocks, 256, 0, h->stream>>>(h->d_io.p, dvec, h->d_api_map.p, n,
                                                    3 * h->plan.Np);
   h->launches++;
   PFC_CUDA(h, cudaGetLastError());

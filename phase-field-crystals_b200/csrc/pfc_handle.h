@@ -81,7 +81,7 @@ struct pfc_handle
   // mesh tables
   pfc::DevBuf<int32_t> d_cell_gather, d_cell_row, d_cell_pos, d_cell_spos, d_cell_col, d_col, d_slave, d_slave_master;
   pfc::DevBuf<double> d_cell_h, d_tab;
-  pfc::DevBuf<int64_t> d_slice_ptr, d_api_map, d_api_gather, d_stress_map, d_owned_map;
+  pfc::DevBuf<int64_t> d_slice_ptr, d_api_map, d_stress_map, d_owned_map;
   pfc::DevBuf<double> d_stress, d_stress_io; // pfc_stress work fields (allocated on first use)
   std::string operator_note;   // why the lattice kernels were declined (pfc_operator_info)
   bool stress_valid = false;
