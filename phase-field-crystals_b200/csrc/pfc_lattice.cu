@@ -164,17 +164,44 @@ namespace
 {
 constexpr int kRingThreads = 128;
 
-// rows per strip: enough CTAs to fill the SMs several times over, strips not shorter than 16 rows (every strip
-// re-reads its 2 HY warm-up rows)
-int ring_rows_per_strip(const pfc_handle *h, int col_blocks, int rows)
+// Rows per strip.  A strip of rs rows costs rs + warm row iterations (warm = the pipeline's warm-up rows, repeated by every
+// strip), and the CTAs run in waves of n_sm x (resident CTAs per SM): the choice minimises waves x (rs + warm) over
+// 16 <= rs <= 64.  Longer strips lose even when they make exactly one wave (the CTAs on the boundary of the owned
+// rectangle take the general index path and finish last: 260 instead of 226 us per sweep on M4 with 317-row strips);
+// shorter ones pay the warm-up too often (profiles/r02u_rs_sweep.log).
+int ring_rows_per_strip(const pfc_handle *h, int col_blocks, int rows, int warm, int resident)
 {
   static const int forced = getenv("PFC_RING_RS") ? atoi(getenv("PFC_RING_RS")) : 0; // tuning aid
   if (forced > 0)
     return forced;
-  int rs = 64; // every strip repeats (2 stages + 2) p warm-up rows; measured on B200 (profiles/r02f_ring_tuning.log)
-  while (rs > 16 && (int64_t)col_blocks * ((rows + rs - 1) / rs) < 8 * (int64_t)h->n_sm)
-    rs /= 2;
-  return rs;
+  const int64_t slots = (int64_t)h->n_sm * std::max(1, resident);
+  int best = 16;
+  int64_t best_cost = INT64_MAX;
+  for (int rs = 16; rs <= std::max(16, std::min(rows, 64)); ++rs)
+    {
+      const int64_t ctas = (int64_t)col_blocks * ((rows + rs - 1) / rs);
+      const int64_t cost = ((ctas + slots - 1) / slots) * (rs + warm);
+      if (cost <= best_cost) // ties: the longer strip
+        best_cost = cost, best = rs;
+    }
+  return best;
+}
+
+// resident CTAs per SM of a kernel (cached per function)
+template <class K>
+int ring_resident(K kernel)
+{
+  static K seen[16];
+  static int occ[16], n_seen = 0;
+  for (int i = 0; i < n_seen; ++i)
+    if (seen[i] == kernel)
+      return occ[i];
+  int nb = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, kRingThreads, 0) != cudaSuccess || nb < 1)
+    nb = 1, cudaGetLastError();
+  if (n_seen < 16)
+    seen[n_seen] = kernel, occ[n_seen++] = nb;
+  return nb;
 }
 
 template <int STAGES, class K1, class K2>
@@ -186,7 +213,8 @@ int ring_launch(pfc_handle *h, RingOp op, const Ctl *ctl, K1 q1, K2 q2)
   if (cols <= 0 || rows <= 0 || op.lo < STAGES * p)
     return h->fail(PFC_ERR_STATE, "ring kernel: window margin %d outside the ring", op.lo);
   const int cb = (cols + outw - 1) / outw;
-  op.rs = ring_rows_per_strip(h, cb, rows);
+  const int warm = 2 * STAGES * p + STAGES - 1; // rows before the first and after the last output row of a strip
+  op.rs = ring_rows_per_strip(h, cb, rows, warm, p == 1 ? ring_resident(q1) : ring_resident(q2));
   const dim3 grid(cb, (rows + op.rs - 1) / op.rs);
   if (p == 1)
     q1<<<grid, kRingThreads, 0, h->stream>>>(G, op, ctl);
