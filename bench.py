@@ -528,7 +528,7 @@ def main():
     # ---- roofline legs on resident data (rank-local kernels) ----
     peak, peak_src = measured_peak()
     ms_per_step = ms_dev / args.steps
-    sweeps = args.sweeps if args.sweeps > 0 else (5 if degree == 2 else (4 if args.mf else 3))  # the library's defaults
+    sweeps = args.sweeps if args.sweeps > 0 else ((6 if degree == 2 else 4) if args.mf else (5 if degree == 2 else 3))  # the library's defaults
     legs = None
     if not args.no_legs:
         solver.assemble()

@@ -96,10 +96,10 @@ extern "C" int pfc_create(const pfc_params *p, pfc_handle **out)
   h->restart = ntmp - 2;
   h->n_basis = ntmp - 1;
   // Chebyshev degree: measured optimum of the lattice path on M2-sized meshes (profiles/README.md): Q2 5, Q1 3
-  // default Chebyshev degree: measured best per path (M2: 5; M4 matrix-free with the cheap streaming sweeps: 4, 226 against
-  // 237 ms per step at 3 or 5, profiles/r02r)
+  // default Chebyshev degree: measured best per path.  Matrix-free lattice path with its cheap streaming sweeps: Q1 4 (M4: 226
+  // against 237 ms per step at 3 or 5, profiles/r02r), Q2 6 (M2: 24.7 against 25.5 ms at 5, profiles/r02x); assembled: 3 / 5
   h->sweeps = p->precond_sweeps > 0 ? p->precond_sweeps
-                                    : (p->degree == 2 ? 5 : (p->operator_kind == PFC_OPERATOR_MATRIX_FREE ? 4 : 3));
+                                    : (p->operator_kind == PFC_OPERATOR_MATRIX_FREE ? (p->degree == 2 ? 6 : 4) : (p->degree == 2 ? 5 : 3));
   int dev = p->device;
   if (dev < 0)
     cudaGetDevice(&dev);

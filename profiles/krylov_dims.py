@@ -20,7 +20,10 @@ Psi0 = mesh.hexagonal_lattice(P.default_A0(B.PSI0, B.EPS), B.PSI0)
 s = P.Solver(degree=a.degree, dt=B.DT, theta=B.THETA, eps=B.EPS, preconditioner=1, operator_kind=1)
 s.setup(mesh)
 s.set_state(Psi0, Psi0)
-s.step()
+if not os.environ.get("SKIP_STEP"):
+    s.step()
+else:
+    s.assemble()
 for dim in [int(x) for x in os.environ.get("DIMS", "4 8 12 14 16 20 24 27").split()]:
     k = s.time_krylov(dim=dim, reps=10)
     print(json.dumps({"dim": dim, "us_dot": 1e3 * k["ms_dot"], "gbs_dot": k["bytes_dot"] / k["ms_dot"] / 1e6,
