@@ -121,16 +121,16 @@ static __global__ void __launch_bounds__(kVecThreads, DIM >= 12 ? 2 : 3)
 template <int DIM>
 static __global__ void __launch_bounds__(kVecThreads, DIM >= 12 ? 2 : 3)
   multiaxpy_kernel(const double *__restrict__ V, int64_t stride, double *__restrict__ w, int64_t n2,
-                   const double *__restrict__ h, double *partial, double *out, unsigned int *counter, Ctl *ctl, int pass,
-                   ArDev ar)
+                   const double *__restrict__ h, const double *__restrict__ is2, double *partial, double *out,
+                   unsigned int *counter, Ctl *ctl, int pass, ArDev ar)
 {
   (void)pass;
   if (ctl->state != 0)
     return;
-  double hh[DIM];
+  double hh[DIM]; // is2: the basis vectors are stored unnormalised (s_i v_i) and h holds (s_i v_i) . w: coefficient h_i / s_i^2
 #pragma unroll
   for (int i = 0; i < DIM; ++i)
-    hh[i] = h[i];
+    hh[i] = is2 ? h[i] * is2[i] : h[i];
   double acc[1] = {0};
   double2 *w2 = reinterpret_cast<double2 *>(w);
   for (int64_t idx = (int64_t)blockIdx.x * kVecThreads + threadIdx.x; idx < n2; idx += (int64_t)gridDim.x * kVecThreads)
@@ -166,6 +166,8 @@ struct GmresSmall
   double dots0[kMaxBasis + 1];     // pass 0: V_i . w, [dim] = w . w
   double dots1[kMaxBasis + 1];     // pass 1
   double nrm2[2];                  // ||w||^2 after pass 0 / pass 1
+  // lazy normalisation (preconditioned solves): basis vector i is stored as s_i v_i, s_0 = 1, s_{j+1} = ||w'_j||
+  double s2[kMaxBasis + 1], is2[kMaxBasis + 1]; // s_i^2 and 1 / s_i^2
 };
 
 // Hessenberg column, Givens rotation, residual estimate, SolverControl::check.
@@ -173,7 +175,7 @@ struct GmresSmall
 // Otherwise the Kelley test [dealii-ext: norm_vv > 10 * norm_vv_start * sqrt(eps)] is applied to the single
 // pass; if it trips, the iteration is discarded and the cycle ends with state 3: the host continues the
 // solve with two-pass cycles (the re-orthogonalisation flag is sticky, as in deal.II).
-static __global__ void givens_kernel(GmresSmall *g, Ctl *ctl, int inner, int two_pass)
+static __global__ void givens_kernel(GmresSmall *g, Ctl *ctl, int inner, int two_pass, int lazy)
 {
   if (ctl->state != 0)
     return;
@@ -192,7 +194,18 @@ static __global__ void givens_kernel(GmresSmall *g, Ctl *ctl, int inner, int two
   double h[kMaxBasis + 1];
   for (int i = 0; i < dim; ++i)
     h[i] = g->dots0[i] + (two_pass ? g->dots1[i] : 0.0);
-  const double s = sqrt(two_pass ? g->nrm2[1] : g->nrm2[0]);
+  const double n2w = two_pass ? g->nrm2[1] : g->nrm2[0];
+  double s = sqrt(n2w);
+  if (lazy)
+    { // Lazy normalisation: the stored vectors are s_i v_i and w is s_j (J P^-1 v_j), so the dots carry s_i s_j and the
+      // norm carries s_j; the new vector stays as it is, s_{j+1} = ||w'|| (no pass over it to divide by its norm).
+      const double isj = sqrt(g->is2[inner]);
+      for (int i = 0; i < dim; ++i)
+        h[i] *= sqrt(g->is2[i]) * isj;
+      g->s2[dim] = n2w;
+      g->is2[dim] = n2w != 0.0 ? 1.0 / n2w : 1.0;
+      s *= isj;
+    }
   h[dim] = s;
   ctl->inv_norm = (s != 0.0) ? 1.0 / s : 1.0;
   for (int i = 0; i < inner; ++i)
@@ -273,6 +286,7 @@ static __global__ void cycle_begin_kernel(GmresSmall *g, Ctl *ctl)
   else if (ctl->iters >= ctl->max_iters || isnan(rho))
     ctl->state = 2;
   g->gamma[0] = rho;
+  g->s2[0] = g->is2[0] = 1.0; // v_0 is normalised by the scale kernel that follows
   ctl->inv_norm = rho != 0.0 ? 1.0 / rho : 1.0;
 }
 
@@ -284,7 +298,7 @@ static __global__ void end_gate_kernel(const Ctl *ctl, Ctl *gate, int restart)
 }
 
 // end of a cycle: back substitution H y = gamma (H1.backward), dim = ctl->dim
-static __global__ void backsolve_kernel(GmresSmall *g, Ctl *ctl, const Ctl *gate)
+static __global__ void backsolve_kernel(GmresSmall *g, Ctl *ctl, const Ctl *gate, int lazy)
 {
   if (gate->state != 0)
     return;
@@ -296,6 +310,9 @@ static __global__ void backsolve_kernel(GmresSmall *g, Ctl *ctl, const Ctl *gate
         s -= g->H[i * kMaxBasis + j] * g->y[j];
       g->y[i] = s / g->H[i * kMaxBasis + i];
     }
+  if (lazy) // x += sum y_i v_i = sum (y_i / s_i) (s_i v_i)
+    for (int i = 0; i < dim; ++i)
+      g->y[i] *= sqrt(g->is2[i]);
 }
 
 // x += sum_{i < dim} y_i V_i ; dim read from the device; consumes the cycle (dim := 0)

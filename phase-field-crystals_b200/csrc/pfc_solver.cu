@@ -180,7 +180,8 @@ static int apply_operator(pfc_handle *h, double *x, double *y, const Ctl *ctl, b
 
 // ---- template dispatch over the Krylov dimension ---------------------------------------------------
 using DotFn = void (*)(const double *, int64_t, const double *, int64_t, double *, double *, unsigned int *, const Ctl *, int, ArDev);
-using AxpyFn = void (*)(const double *, int64_t, double *, int64_t, const double *, double *, double *, unsigned int *, Ctl *, int, ArDev);
+using AxpyFn = void (*)(const double *, int64_t, double *, int64_t, const double *, const double *, double *, double *, unsigned int *, Ctl *,
+                        int, ArDev);
 constexpr int kMaxDim = 32;
 template <int D>
 struct Tab
@@ -254,6 +255,10 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0,
   // peer-memory path: the reduction kernels all-reduce their results in their last block (no collective kernel)
   const ArDev ar = comm_ar_endpoint(h);
   const bool fused = ar.R > 1;
+  // Lazy normalisation of the basis (GmresSmall::s2): no scale pass per iteration.  Preconditioned solves only; the
+  // unpreconditioned path keeps the arithmetic of deal.II's SolverGMRES (its iteration counts are compared with the oracle's).
+  const bool lazy = precond;
+  const double *is2 = lazy ? g->is2 : nullptr;
 
   if (i0 == 0)
     {
@@ -284,7 +289,7 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0,
       g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots0, cnt, ctl, 0, ar);
       if (!fused)
         PFC_TRY(allreduce_sum(h, g->dots0, dim + 1, ctl));
-      g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, st, w, n2, g->dots0, partial, &g->nrm2[0], cnt, ctl, 0, ar);
+      g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, st, w, n2, g->dots0, is2, partial, &g->nrm2[0], cnt, ctl, 0, ar);
       if (!fused)
         PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1, ctl));
       if (two_pass)
@@ -292,18 +297,19 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0,
           g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots1, cnt, ctl, 1, ar);
           if (!fused)
             PFC_TRY(allreduce_sum(h, g->dots1, dim + 1, ctl));
-          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, st, w, n2, g->dots1, partial, &g->nrm2[1], cnt, ctl, 1, ar);
+          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, st, w, n2, g->dots1, is2, partial, &g->nrm2[1], cnt, ctl, 1, ar);
           if (!fused)
             PFC_TRY(allreduce_sum(h, &g->nrm2[1], 1, ctl));
           h->launches += 2;
         }
-      givens_kernel<<<1, 1, 0, s>>>(g, ctl, inner, two_pass ? 1 : 0);
-      scale_kernel<<<grid, kVecThreads, 0, s>>>(w, n2, ctl);
-      h->launches += 5;
+      givens_kernel<<<1, 1, 0, s>>>(g, ctl, inner, two_pass ? 1 : 0, lazy ? 1 : 0);
+      if (!lazy)
+        scale_kernel<<<grid, kVecThreads, 0, s>>>(w, n2, ctl);
+      h->launches += lazy ? 4 : 5;
     }
   // end part: runs when the solve has stopped or the restart length is reached, else the continuation piece follows
   end_gate_kernel<<<1, 1, 0, s>>>(ctl, gate, h->restart);
-  backsolve_kernel<<<1, 1, 0, s>>>(g, ctl, gate);
+  backsolve_kernel<<<1, 1, 0, s>>>(g, ctl, gate, lazy ? 1 : 0);
   if (precond)
     { // x += P^-1 (V y)
       PFC_CUDA(h, cudaMemsetAsync(h->d_u.p, 0, 3 * P.Np * sizeof(double), s));
@@ -686,13 +692,13 @@ extern "C" int pfc_time_krylov(pfc_handle *h, int32_t dim, int32_t reps, double 
         if (k == 0)
           g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0, ArDev{});
         else
-          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
+          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, nullptr, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
       PFC_CUDA(h, cudaEventRecord(h->ev[0], s));
       for (int i = 0; i < reps; ++i)
         if (k == 0)
           g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0, ArDev{});
         else
-          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
+          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, nullptr, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
       h->launches += reps + 2;
       PFC_CUDA(h, cudaEventRecord(h->ev[1], s));
       PFC_CUDA(h, cudaStreamSynchronize(s));
