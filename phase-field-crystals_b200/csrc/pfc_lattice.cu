@@ -247,6 +247,15 @@ static bool ring_deep(bool dflt)
 int ring_launch_t(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(1, ring_t_kernel, true, false) }
 int ring_launch_sweep(pfc_handle *h, const RingOp &op, const Ctl *ctl)
 {
+  static const int staged = getenv("PFC_SWEEP_STAGED") ? atoi(getenv("PFC_SWEEP_STAGED")) : 4; // 0: off; 3, 4, 6: distance
+  if (h->plan.degree == 1 && h->q1_fast && op.epi == 0 && staged > 0) // Chebyshev step: operands staged by cp.async
+    {
+      if (staged == 3)
+        return ring_launch<3>(h, op, ctl, ring_sweep1a_kernel<kRingThreads, 3>, ring_sweep1a_kernel<kRingThreads, 3>);
+      if (staged == 6)
+        return ring_launch<3>(h, op, ctl, ring_sweep1a_kernel<kRingThreads, 6>, ring_sweep1a_kernel<kRingThreads, 6>);
+      return ring_launch<3>(h, op, ctl, ring_sweep1a_kernel<kRingThreads, 4>, ring_sweep1a_kernel<kRingThreads, 4>);
+    }
   PFC_RING_DISPATCH1(3, ring_sweep1_kernel, true)
   PFC_RING_DISPATCH(3, ring_sweep_kernel, true, false)
 }

@@ -96,6 +96,20 @@ __device__ __forceinline__ void ysum(const Cst &C, int j, const double (&wk)[3],
 }
 } // namespace q1
 
+// cp.async (LDGSTS), 8 bytes: global -> shared without a register in between
+__device__ __forceinline__ void cp_async8(double *smem_dst, const double *gsrc)
+{
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait()
+{
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
+
 // ---- fused t kernel + Schur right-hand side + first Chebyshev step (Q1) -------------------------------------------
 // A thread owns node column X and the cell column between X and X + 1.  Iteration n: publish m1(n) = r1(n) / ml,
 // t(n - 2), psi_n(n) and the hand-over of the cell formed in iteration n - 1;  K m1 (n - 1) -> t(n - 1);  D t (n - 3);
@@ -335,6 +349,110 @@ static __global__ void __launch_bounds__(NT) ring_sweep1_kernel(LatGeom L, RingO
     ring_sweep1_rows<NT, PF, false>(L, O, s_ex, s_del, X0 + tid, Y0, Y1);
 }
 
+// ---- the same sweep with its operands staged by cp.async (epi 0, interior CTAs) -------------------------------------
+// ring_sweep1_kernel prefetches rows into registers: 150 registers, 12 warps per SM, and a warp that waits for its
+// oldest load also waits for the newest ones (6 scoreboards).  Here every thread copies its element of x(n + D) and of
+// rhs, dinv, d of the output row of iteration n + D straight into shared-memory rings (LDGSTS, no register, no
+// scoreboard), one commit group per row; wait_group<D> + the row's __syncthreads make row n visible.  x lands directly
+// in the exchange row its neighbours read.  CTAs on the boundary of the owned rectangle run ring_sweep1_rows.
+// D = prefetch distance in rows; ring depths: x D + 7 (> D + 5: the output row is read again as x_old), operands D + 1
+template <int NT, int D>
+static __global__ void __launch_bounds__(NT) ring_sweep1a_kernel(LatGeom L, RingOp O, const Ctl *ctl)
+{
+  if (ctl && ctl->state != 0)
+    return;
+  constexpr int HX = 3, OUTW = NT - 2 * HX, RX = D + 7, RO = D + 1;
+  constexpr int N_X = RX * (NT + 2), N_OP = 3 * RO * NT, N_EX = 2 * 2 * (NT + 2), N_DEL = 4 * NT;
+  __shared__ double raw[N_X + N_OP + N_EX + N_DEL];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < N_X + N_OP + N_EX + N_DEL; i += NT)
+    raw[i] = 0.0;
+  const int X0 = O.lo + blockIdx.x * OUTW - HX;
+  const int Y0 = O.lo + blockIdx.y * O.rs, Y1 = min(Y0 + O.rs, L.fh - O.lo);
+  __syncthreads();
+  if (!ring_cta_fast(L, X0, NT, Y0 - HX, Y1 - 1 + HX))
+    { // general index path, register prefetch
+      double(&s_ex)[2][3][NT + 2] = *reinterpret_cast<double(*)[2][3][NT + 2]>(raw);
+      double(&s_del)[4][NT] = *reinterpret_cast<double(*)[4][NT]>(raw + 2 * 3 * (NT + 2));
+      ring_sweep1_rows<NT, 1, false>(L, O, s_ex, s_del, X0 + tid, Y0, Y1);
+      return;
+    }
+  double(&s_x)[RX][NT + 2] = *reinterpret_cast<double(*)[RX][NT + 2]>(raw);
+  double(&s_op)[3][RO][NT] = *reinterpret_cast<double(*)[3][RO][NT]>(raw + N_X);
+  double(&s_ex)[2][2][NT + 2] = *reinterpret_cast<double(*)[2][2][NT + 2]>(raw + N_X + N_OP);
+  double(&s_del)[4][NT] = *reinterpret_cast<double(*)[4][NT]>(raw + N_X + N_OP + N_EX);
+  const q1::Cst C(L);
+  const bool outcol = tid >= HX && tid < NT - HX;
+  const double iml = L.ihx * L.ihy, c0 = O.cheb[0], c1 = O.cheb[1];
+  const int w = L.w;
+  const int64_t base = (int64_t)(X0 + tid - L.ex0) - (int64_t)L.ey0 * w; // id of (X, Y) = base + Y w
+  const double *xp = O.x + base;                                        // x_vec: component 0 of a vector = the same address
+  double *outp = O.out + base;
+  const int n0 = Y0 - HX, nx1 = Y1 - 1 + HX, n1 = nx1 + 2;
+  // one commit group per row: x(n) and the operands of the output row n - 5
+  auto issue = [&](int n) {
+    if (n <= nx1)
+      cp_async8(&s_x[(n - n0) % RX][tid + 1], xp + (int64_t)n * w);
+    const int m = n - 5;
+    if (outcol && m >= Y0 && m < Y1)
+      {
+        const int so = (n - n0) % RO;
+        const int64_t r = base + (int64_t)m * w;
+        cp_async8(&s_op[0][so][tid], O.rhs + r);
+        cp_async8(&s_op[1][so][tid], O.dinv + r);
+        cp_async8(&s_op[2][so][tid], O.d + r);
+      }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int k = 0; k < D; ++k)
+    issue(n0 + k);
+  double w1k[3] = {0, 0, 0}, w1m[3] = {0, 0, 0}, w2k[3] = {0, 0, 0}, w2m[3] = {0, 0, 0}, w3k[3] = {0, 0, 0}, w3m[3] = {0, 0, 0};
+  double a1 = 0, a2 = 0;
+  int dl = 0;
+  for (int nb = n0; nb <= n1; nb += 3)
+    {
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+        {
+          const int n = nb + j;
+          if (n > n1)
+            break;
+          issue(n + D);
+          const int par = (n - n0) & 1, sx = (n - n0) % RX;
+          s_ex[par][0][tid + 1] = a1;
+          s_ex[par][1][tid + 1] = a2;
+          cp_async_wait<D>();
+          __syncthreads();
+          double Kv, Mv;
+          if (n <= nx1)
+            q1::xsum(&s_x[sx][tid], w1k[j], w1m[j]); // x, row n
+          else
+            w1k[j] = w1m[j] = 0.0;
+          q1::xsum(&s_ex[par][0][tid], w2k[j], w2m[j]); // t1, row n - 2
+          q1::xsum(&s_ex[par][1][tid], w3k[j], w3m[j]); // t2, row n - 4
+          q1::ysum<true>(C, j, w1k, w1m, Kv, Mv);       // t1 = M_L^-1 K x at row n - 1; (M x) waits for its output row
+          a1 = Kv * iml;
+          const double Mx_m = s_del[dl][tid];
+          s_del[dl][tid] = Mv;
+          dl = (dl + 1) & 3;
+          q1::ysum<false>(C, j, w2k, w2m, Kv, Mv);      // t2 = M_L^-1 K t1 at row n - 3
+          a2 = Kv * iml;
+          const int m = n - 5;
+          if (outcol && m >= Y0 && m < Y1)
+            {
+              q1::ysum<true>(C, j, w3k, w3m, Kv, Mv);   // K t2, M t2 at the output row
+              const double Sx = O.bbar * Mx_m + O.dtth * fma(-2.0, Mv, Kv);
+              const int so = (n - n0) % RO;
+              const double dn = c0 * s_op[2][so][tid] + c1 * s_op[1][so][tid] * (s_op[0][so][tid] - Sx);
+              const int64_t r = (int64_t)m * w;
+              O.d[base + r] = dn;
+              outp[r] = s_x[(m - n0) % RX][tid + 1] + dn;
+            }
+        }
+    }
+}
+
 // ---- back substitution, Q1 closed form (pipeline of ring_back_kernel) -----------------------------------------------
 template <int NT, int PF, bool FAST>
 __device__ __forceinline__ void ring_back1_rows(const LatGeom &L, const RingOp &O, double (&s_ex)[2][2][NT + 2], int X,
@@ -425,18 +543,6 @@ static __global__ void __launch_bounds__(NT) ring_back1_kernel(LatGeom L, RingOp
 // the other resident CTAs (measured: 522 -> 510 us), so a CTA walks over NTILE tiles of a tile row and stages the
 // nodal values of the next tile with cp.async (LDGSTS, 8 bytes: a tile row starts at any node) while it works on the
 // current one; two shared-memory buffers.  NTILE = 1: plain version, no pipeline.
-__device__ __forceinline__ void cp_async8(double *smem_dst, const double *gsrc)
-{
-  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(d), "l"(gsrc) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait()
-{
-  asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
-}
-
 template <int CX, int CY, int NTILE, int MINB>
 static __global__ void __launch_bounds__(CX *CY, MINB) lat_j1_kernel(LatGeom L, LatOp O, const Ctl *ctl)
 {
