@@ -261,6 +261,9 @@ int ring_launch_sweep(pfc_handle *h, const RingOp &op, const Ctl *ctl)
 }
 int ring_launch_back(pfc_handle *h, const RingOp &op, const Ctl *ctl)
 {
+  static const int staged = getenv("PFC_BACK_STAGED") ? atoi(getenv("PFC_BACK_STAGED")) : 4; // 0: off (tuning / A-B aid)
+  if (h->plan.degree == 1 && h->q1_fast && staged > 0)
+    return ring_launch<2>(h, op, ctl, ring_back1a_kernel<kRingThreads, 4>, ring_back1a_kernel<kRingThreads, 4>);
   PFC_RING_DISPATCH1(2, ring_back1_kernel, false)
   PFC_RING_DISPATCH(2, ring_back_kernel, false, false)
 }
@@ -268,6 +271,9 @@ int ring_launch_rhs1(pfc_handle *h, const RingOp &op, const Ctl *ctl)
 {
   if (h->plan.degree != 1)
     return h->fail(PFC_ERR_UNSUPPORTED, "ring_launch_rhs1 is a Q1 kernel");
+  static const int staged = getenv("PFC_RHS_STAGED") ? atoi(getenv("PFC_RHS_STAGED")) : 4; // 0: off (tuning / A-B aid)
+  if (staged > 0)
+    return ring_launch<2>(h, op, ctl, ring_rhs1a_kernel<kRingThreads, 4>, ring_rhs1a_kernel<kRingThreads, 4>);
   return ring_launch<2>(h, op, ctl, ring_rhs1_kernel<kRingThreads>, ring_rhs1_kernel<kRingThreads>);
 }
 #undef PFC_RING_DISPATCH1

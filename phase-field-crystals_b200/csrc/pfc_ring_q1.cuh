@@ -535,6 +535,205 @@ static __global__ void __launch_bounds__(NT) ring_back1_kernel(LatGeom L, RingOp
     ring_back1_rows<NT, PF, false>(L, O, s_ex, X0 + tid, Y0, Y1);
 }
 
+// ---- fused right-hand side kernel and back substitution with cp.async staging (interior CTAs), as ring_sweep1a_kernel --
+template <int NT, int D>
+static __global__ void __launch_bounds__(NT) ring_rhs1a_kernel(LatGeom L, RingOp O, const Ctl *ctl)
+{
+  if (ctl && ctl->state != 0)
+    return;
+  constexpr int HX = 2, OUTW = NT - 2 * HX, RX = D + 2, RO = D + 1;
+  constexpr int N_X = 2 * RX * (NT + 2), N_OP = 3 * RO * NT, N_EX = 2 * 2 * (NT + 2), N_SLOW = 2 * 4 * (NT + 2);
+  constexpr int N_RAW = N_X + N_OP + N_EX > N_SLOW ? N_X + N_OP + N_EX : N_SLOW;
+  __shared__ double raw[N_RAW];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < N_RAW; i += NT)
+    raw[i] = 0.0;
+  const int X0 = O.lo + blockIdx.x * OUTW - HX;
+  const int Y0 = O.lo + blockIdx.y * O.rs, Y1 = min(Y0 + O.rs, L.fh - O.lo);
+  __syncthreads();
+  if (!ring_cta_fast(L, X0, NT, Y0 - HX, Y1 + 1))
+    {
+      double(&s_ex)[2][4][NT + 2] = *reinterpret_cast<double(*)[2][4][NT + 2]>(raw);
+      ring_rhs1_rows<NT, false>(L, O, s_ex, X0 + tid, Y0, Y1);
+      return;
+    }
+  double(&s_x)[2][RX][NT + 2] = *reinterpret_cast<double(*)[2][RX][NT + 2]>(raw); // r1, psi_n: rows n .. n + D
+  double(&s_op)[3][RO][NT] = *reinterpret_cast<double(*)[3][RO][NT]>(raw + N_X);  // r2(n - 1), r0(n - 3), dinv(n - 3)
+  double(&s_ex)[2][2][NT + 2] = *reinterpret_cast<double(*)[2][2][NT + 2]>(raw + N_X + N_OP); // t(n - 2), hand-over
+  const q1::Cst C(L);
+  const bool outcol = tid >= HX && tid < NT - HX;
+  const double iml = L.ihx * L.ihy, jxw = 0.25 * L.hx * L.hy;
+  const double cm0 = -O.dtth * (1.0 + O.eps), cm2 = -3.0 * O.dtth, cheb0 = O.cheb[0];
+  const int w = L.w, Np = (int)L.Np;
+  const int64_t base = (int64_t)(X0 + tid - L.ex0) - (int64_t)L.ey0 * w; // id of (X, Y) = base + Y w
+  const int n0 = Y0 - HX, nl1 = Y1 + 1, n1 = Y1 + 2;
+  auto issue = [&](int n) {
+    const int sx = (n - n0) % RX, so = (n - n0) % RO;
+    if (n <= nl1)
+      {
+        const int64_t r = base + (int64_t)n * w;
+        cp_async8(&s_x[0][sx][tid + 1], O.in + Np + r);
+        cp_async8(&s_x[1][sx][tid + 1], O.psi + r);
+      }
+    if (n - 1 >= n0 && n - 1 <= nl1 - 1)
+      cp_async8(&s_op[0][so][tid], O.in + 2 * (int64_t)Np + base + (int64_t)(n - 1) * w);
+    const int m = n - 3;
+    if (outcol && m >= Y0 && m < Y1)
+      {
+        const int64_t r = base + (int64_t)m * w;
+        cp_async8(&s_op[1][so][tid], O.in + r);
+        cp_async8(&s_op[2][so][tid], O.dinv + r);
+      }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int k = 0; k < D; ++k)
+    issue(n0 + k);
+  double w0k[3] = {0, 0, 0}, w0m[3] = {0, 0, 0}, w1k[3] = {0, 0, 0}, w1m[3] = {0, 0, 0};
+  double tpub = 0, rpub = 0;
+  q1::XS m_top = {0, 0, 0}, p_top = {0, 0, 0};
+  double c01p = 0, c11p = 0, Pprev = 0, Vhold = 0;
+  for (int nb = n0; nb <= n1; nb += 3)
+    {
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+        {
+          const int n = nb + j;
+          if (n > n1)
+            break;
+          issue(n + D);
+          const int par = (n - n0) & 1, sx = (n - n0) % RX, so = (n - n0) % RO;
+          s_ex[par][0][tid + 1] = tpub;
+          s_ex[par][1][tid + 1] = rpub;
+          cp_async_wait<D>();
+          __syncthreads();
+          const bool have = n <= nl1; // rows beyond the last one needed count as zero
+          const double m1L = have ? s_x[0][sx][tid] * iml : 0.0, m1n = have ? s_x[0][sx][tid + 1] * iml : 0.0;
+          const double m1R = have ? s_x[0][sx][tid + 2] * iml : 0.0;
+          const double psn = have ? s_x[1][sx][tid + 1] : 0.0, psR = have ? s_x[1][sx][tid + 2] : 0.0;
+          {
+            const double sm = m1L + m1R;
+            w0k[j] = fma(2.0, m1n, -sm);
+            w0m[j] = fma(4.0, m1n, sm);
+          }
+          double Kv, Mv;
+          q1::ysum<false>(C, j, w0k, w0m, Kv, Mv); // K m1 at row n - 1
+          const bool t_ok = n - 1 >= n0 && n - 1 <= nl1 - 1;
+          tpub = t_ok ? iml * (s_op[0][so][tid] - Kv) : 0.0; // t(n - 1)
+          q1::xsum(&s_ex[par][0][tid], w1k[j], w1m[j]);     // t, row n - 2
+          q1::ysum<true>(C, j, w1k, w1m, Kv, Mv);          // K t, M t at row n - 3
+          const double Dt = O.dtth * fma(-2.0, Mv, Kv);
+          const q1::XS m_bot = q1::xstage(m1n, m1R), p_bot = q1::xstage(psn, psR);
+          double mv[2][2], pv[2][2], dy[2], Aq[2][2], c[2][2];
+          q1::values(m_top, m_bot, mv, dy);
+          q1::values(p_top, p_bot, pv, dy);
+#pragma unroll
+          for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+              Aq[a][b] = fma(cm2 * pv[a][b], pv[a][b], cm0) * mv[a][b];
+          q1::test(Aq, c);
+          m_top = m_bot;
+          p_top = p_bot;
+          const double Pnew = c[0][0] + c01p;
+          rpub = c[0][1] + c11p;
+          c01p = c[1][0];
+          c11p = c[1][1];
+          const double Vuse = Vhold;
+          Vhold = Pprev + s_ex[par][1][tid];
+          Pprev = Pnew;
+          const int m = n - 3;
+          if (outcol && m >= Y0 && m < Y1)
+            {
+              const double rhs = s_op[1][so][tid] - jxw * Vuse - Dt;
+              const double x0 = cheb0 * s_op[2][so][tid] * rhs;
+              const int64_t r = base + (int64_t)m * w;
+              O.out[r] = rhs;
+              O.d[r] = x0;
+              O.out2[r] = x0;
+            }
+        }
+    }
+}
+
+template <int NT, int D>
+static __global__ void __launch_bounds__(NT) ring_back1a_kernel(LatGeom L, RingOp O, const Ctl *ctl)
+{
+  if (ctl && ctl->state != 0)
+    return;
+  constexpr int HX = 2, OUTW = NT - 2 * HX, RX = D + 2, RO = D + 1;
+  constexpr int N_X = RX * (NT + 2), N_OP = 2 * RO * NT, N_EX = 2 * (NT + 2), N_SLOW = 2 * 2 * (NT + 2);
+  constexpr int N_RAW = N_X + N_OP + N_EX > N_SLOW ? N_X + N_OP + N_EX : N_SLOW;
+  __shared__ double raw[N_RAW];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < N_RAW; i += NT)
+    raw[i] = 0.0;
+  const int X0 = O.lo + blockIdx.x * OUTW - HX;
+  const int Y0 = O.lo + blockIdx.y * O.rs, Y1 = min(Y0 + O.rs, L.fh - O.lo);
+  __syncthreads();
+  if (!ring_cta_fast(L, X0, NT, Y0 - HX, Y1 - 1 + HX + 1))
+    {
+      double(&s_ex)[2][2][NT + 2] = *reinterpret_cast<double(*)[2][2][NT + 2]>(raw);
+      ring_back1_rows<NT, 1, false>(L, O, s_ex, X0 + tid, Y0, Y1);
+      return;
+    }
+  double(&s_x)[RX][NT + 2] = *reinterpret_cast<double(*)[RX][NT + 2]>(raw);       // psi (component 0 of z): rows n .. n + D
+  double(&s_op)[2][RO][NT] = *reinterpret_cast<double(*)[2][RO][NT]>(raw + N_X);  // r1(n - 1), r2(n - 3)
+  double(&s_ex)[2][NT + 2] = *reinterpret_cast<double(*)[2][NT + 2]>(raw + N_X + N_OP); // chi(n - 2)
+  const q1::Cst C(L);
+  const bool outcol = tid >= HX && tid < NT - HX;
+  const double iml = L.ihx * L.ihy;
+  const int w = L.w, Np = (int)L.Np;
+  const int64_t base = (int64_t)(X0 + tid - L.ex0) - (int64_t)L.ey0 * w;
+  const int n0 = Y0 - HX, nx1 = Y1 - 1 + HX, n1 = nx1 + 1;
+  auto issue = [&](int n) {
+    const int sx = (n - n0) % RX, so = (n - n0) % RO;
+    if (n <= nx1)
+      cp_async8(&s_x[sx][tid + 1], O.z + base + (int64_t)n * w);
+    if (n - 1 >= n0 && n <= n1)
+      cp_async8(&s_op[0][so][tid], O.in + Np + base + (int64_t)(n - 1) * w);
+    const int m = n - 3;
+    if (outcol && m >= Y0 && m < Y1)
+      cp_async8(&s_op[1][so][tid], O.in + 2 * (int64_t)Np + base + (int64_t)m * w);
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int k = 0; k < D; ++k)
+    issue(n0 + k);
+  double w1k[3] = {0, 0, 0}, w1m[3] = {0, 0, 0}, w2k[3] = {0, 0, 0}, w2m[3] = {0, 0, 0};
+  double a1 = 0;
+  for (int nb = n0; nb <= n1; nb += 3)
+    {
+#pragma unroll
+      for (int j = 0; j < 3; ++j)
+        {
+          const int n = nb + j;
+          if (n > n1)
+            break;
+          issue(n + D);
+          const int par = (n - n0) & 1, sx = (n - n0) % RX, so = (n - n0) % RO, mc = n - 1, m = n - 3;
+          s_ex[par][tid + 1] = a1;
+          cp_async_wait<D>();
+          __syncthreads();
+          double Kv, Mv;
+          if (n <= nx1)
+            q1::xsum(&s_x[sx][tid], w1k[j], w1m[j]); // psi, row n
+          else
+            w1k[j] = w1m[j] = 0.0;
+          q1::xsum(&s_ex[par][tid], w2k[j], w2m[j]); // chi, row n - 2
+          q1::ysum<false>(C, j, w1k, w1m, Kv, Mv);
+          a1 = (mc >= n0) ? iml * (s_op[0][so][tid] - Kv) : 0.0;
+          if (outcol && mc >= Y0 && mc < Y1)
+            O.z[Np + base + (int64_t)mc * w] = a1;
+          if (outcol && m >= Y0 && m < Y1)
+            {
+              q1::ysum<false>(C, j, w2k, w2m, Kv, Mv);
+              O.z[2 * (int64_t)Np + base + (int64_t)m * w] = iml * (s_op[1][so][tid] - Kv);
+            }
+        }
+    }
+}
+
 // ---- J apply on tiles of cells (Q1) ---------------------------------------------------------------------------------
 // y = J z on the owned nodes.  Tiling as lat_kernel<1, LAT_J> (one thread per cell, the nodes of the inner
 // (CX-1) x (CY-1) cells are the tile's own), but only B z_psi + C z_chi goes through the Gauss points (q1:: algebra);
