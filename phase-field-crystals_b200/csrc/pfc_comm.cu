@@ -612,6 +612,13 @@ int comm_p2p_setup(pfc_handle *h)
   std::memset(&mine, 0, sizeof(mine));
   const char *env = getenv("PFC_NO_P2P");
   bool ok = R <= kMaxRanksP2P && !(env && atoi(env) != 0);
+  // The two-parity LL buffer is paced by the two-way traffic of a pair: a rank cannot send exchange n + 2 to a peer before
+  // it has received n + 1 from it.  A pair with data in one direction only has no such pacing, so any such pair on any
+  // rank keeps ALL ranks on NCCL (the ring overlay makes every pair two-way with a dummy value, pfc_ring_plan.cpp; the
+  // general ghost lists of the assembled path are symmetric on every mesh make_grid produces, but nothing enforces it).
+  for (size_t p = 0; p < P.peers.size() && ok; ++p)
+    if ((P.recv_ptr[p + 1] - P.recv_ptr[p] > 0) != (P.send_ptr[p + 1] - P.send_ptr[p] > 0))
+      ok = false;
   P2PState *S = new P2PState();
   S->R = R;
   S->me = me;

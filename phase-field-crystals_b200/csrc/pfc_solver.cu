@@ -256,7 +256,7 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0,
   const ArDev ar = comm_ar_endpoint(h);
   const bool fused = ar.R > 1;
   // Lazy normalisation of the basis (GmresSmall::s2): no scale pass per iteration.  Preconditioned solves only; the
-  // unpreconditioned path keeps the arithmetic of deal.II's SolverGMRES (its iteration counts are compared with the oracle's).
+  // unpreconditioned path keeps the arithmetic of deal.II's SolverGMRES (the tests compare its iteration counts with the CPU restatement's).
   const bool lazy = precond;
   const double *is2 = lazy ? g->is2 : nullptr;
 
