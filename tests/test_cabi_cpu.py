@@ -36,3 +36,15 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")) or f == "Makefile":
                 txt = open(os.path.join(dp, f)).read()
                 assert "oracle" not in txt.replace("no oracle", ""), os.path.join(dp, f)
+
+
+def test_dealii_adapter_uses_only_declared_entry_points():
+    """integration/pfc_dealii_adapter.cc cannot be compiled here (no deal.II): at least every C-ABI function
+    and constant it names must exist in include/pfc_b200.h."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "pfc_b200.h")).read()
+    src = open(os.path.join(root, "integration", "pfc_dealii_adapter.cc")).read() + open(os.path.join(root, "integration", "pfc_dealii_adapter.h")).read()
+    names = set(re.findall(r"\b(pfc_[a-z_0-9]+|PFC_[A-Z_0-9]+)\b", src)) - {"pfc_b200", "pfc_b200_dealii_adapter", "pfc_dealii_adapter"}
+    missing = [n for n in sorted(names) if not re.search(r"\b" + n + r"\b", hdr)]
+    assert not missing, missing

@@ -464,6 +464,46 @@ def test_shipped_toml_run_end_to_end(built, tmp_path):
     sim.close()
 
 
+def test_native_driver_runs_the_shipped_toml(built, tmp_path):
+    """The C++ driver csrc/pfc_sim.cpp (the stand-in for app/simulations/phase_field_crystal_simulation_mpi.cpp:15-183 +
+    PhaseFieldCrystalSystemMPI::run, mpi.cpp:650-711) on the GPU: the shipped parameter file, one timestep; the VTU it
+    writes equals the committed oracle state after step 1 (psi rel L2 <= 1e-9) and the pcout lines are the reference's."""
+    import os
+    import subprocess
+    from test_simulation_cpu import SHIPPED
+    from vtu_reader import read_piece
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "phase-field-crystals_b200", "pfc_sim")
+    assert os.path.exists(exe), "pfc_sim is built by __graft_entry__.build()"
+    d = str(tmp_path) + os.sep
+    text = []
+    for line in SHIPPED.splitlines():
+        key = line.split("=")[0].strip()
+        if key == "data_folder":
+            line = f'data_folder = "{d}"'
+        elif key == "n_timesteps":
+            line = "n_timesteps = 1"
+        elif key == "output_interval":
+            line = "output_interval = 1"
+        text.append(line)
+    toml = os.path.join(d, "run.toml")
+    with open(toml, "w") as f:
+        f.write("\n".join(text) + "\n")
+    r = subprocess.run([exe, toml], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    for s_ in ("Making grid!", "Iterating timestep: 1", "Residual is: ", "Number of iterations: ", "Number of stress iterations: "):
+        assert s_ in r.stdout, s_
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "config1_step1.npz"))
+    st = built.StandIn(1, 6, (-6 * A, -5 * A), (6 * A, 5 * A))
+    key = {tuple(np.round(p, 9)): t for t, p in enumerate(st.support)}
+    pc = read_piece(d + "phase_field_01.0.vtu")
+    node = np.array([key[tuple(np.round(p[:2], 9))] for p in pc["points"]])
+    for name in ("psi", "chi", "phi"):
+        assert _rel(pc["point_data"][name], g[name][node]) <= 1e-9, name
+    assert os.path.exists(d + "stress_00.0.vtu") and os.path.exists(d + "phase_field_rhs_01.0.vtu")
+    st.close()
+
+
 @pytest.mark.parametrize("degree,n_refines,sweeps", [(1, 6, 0), (2, 5, 0), (2, 7, 0), (1, 3, 2), (2, 2, 1), (1, 8, 4)])
 def test_ring_smoother_and_selfchecks(built, degree, n_refines, sweeps):
     """The streaming Chebyshev sweep (csrc/pfc_ring.cuh) against the composition of the K-stencil and mass-stencil kernels;
