@@ -370,34 +370,37 @@ static __global__ void __launch_bounds__(NT) ring_sweep1a_kernel(LatGeom L, Ring
   const int X0 = O.lo + blockIdx.x * OUTW - HX;
   const int Y0 = O.lo + blockIdx.y * O.rs, Y1 = min(Y0 + O.rs, L.fh - O.lo);
   __syncthreads();
-  if (!ring_cta_fast(L, X0, NT, Y0 - HX, Y1 - 1 + HX))
-    { // general index path, register prefetch
-      double(&s_ex)[2][3][NT + 2] = *reinterpret_cast<double(*)[2][3][NT + 2]>(raw);
-      double(&s_del)[4][NT] = *reinterpret_cast<double(*)[4][NT]>(raw + 2 * 3 * (NT + 2));
-      ring_sweep1_rows<NT, 1, false>(L, O, s_ex, s_del, X0 + tid, Y0, Y1);
-      return;
-    }
+  // interior CTAs address by arithmetic; CTAs that touch the ring take the general index for the ADDRESSES only (same pipeline)
+  const bool fast = ring_cta_fast(L, X0, NT, Y0 - HX, Y1 - 1 + HX);
+  const int X = X0 + tid;
+  const bool colok = fast || (X >= 0 && X < L.fw);
   double(&s_x)[RX][NT + 2] = *reinterpret_cast<double(*)[RX][NT + 2]>(raw);
   double(&s_op)[3][RO][NT] = *reinterpret_cast<double(*)[3][RO][NT]>(raw + N_X);
   double(&s_ex)[2][2][NT + 2] = *reinterpret_cast<double(*)[2][2][NT + 2]>(raw + N_X + N_OP);
   double(&s_del)[4][NT] = *reinterpret_cast<double(*)[4][NT]>(raw + N_X + N_OP + N_EX);
   const q1::Cst C(L);
-  const bool outcol = tid >= HX && tid < NT - HX;
+  const bool outcol = tid >= HX && tid < NT - HX && (fast || X < L.fw - O.lo);
   const double iml = L.ihx * L.ihy, c0 = O.cheb[0], c1 = O.cheb[1];
   const int w = L.w;
-  const int64_t base = (int64_t)(X0 + tid - L.ex0) - (int64_t)L.ey0 * w; // id of (X, Y) = base + Y w
-  const double *xp = O.x + base;                                        // x_vec: component 0 of a vector = the same address
-  double *outp = O.out + base;
+  const int64_t base = (int64_t)(X - L.ex0) - (int64_t)L.ey0 * w; // owned node (X, Y): id = base + Y w
+  const bool xv = O.x_vec, ov = O.out_vec;
+  auto sid = [&](int Y) { return fast ? base + (int64_t)Y * w : (int64_t)lat_id(L, X, Y); }; // index in a scalar field
+  auto xid = [&](int Y) { return (fast || !xv) ? sid(Y) : ring_vaddr(L, X, Y, 0); };         // x: scalar field or component 0
   const int n0 = Y0 - HX, nx1 = Y1 - 1 + HX, n1 = nx1 + 2;
   // one commit group per row: x(n) and the operands of the output row n - 5
   auto issue = [&](int n) {
     if (n <= nx1)
-      cp_async8(&s_x[(n - n0) % RX][tid + 1], xp + (int64_t)n * w);
+      {
+        if (colok)
+          cp_async8(&s_x[(n - n0) % RX][tid + 1], O.x + xid(n));
+        else
+          s_x[(n - n0) % RX][tid + 1] = 0.0;
+      }
     const int m = n - 5;
     if (outcol && m >= Y0 && m < Y1)
       {
         const int so = (n - n0) % RO;
-        const int64_t r = base + (int64_t)m * w;
+        const int64_t r = sid(m);
         cp_async8(&s_op[0][so][tid], O.rhs + r);
         cp_async8(&s_op[1][so][tid], O.dinv + r);
         cp_async8(&s_op[2][so][tid], O.d + r);
@@ -445,9 +448,9 @@ static __global__ void __launch_bounds__(NT) ring_sweep1a_kernel(LatGeom L, Ring
               const double Sx = O.bbar * Mx_m + O.dtth * fma(-2.0, Mv, Kv);
               const int so = (n - n0) % RO;
               const double dn = c0 * s_op[2][so][tid] + c1 * s_op[1][so][tid] * (s_op[0][so][tid] - Sx);
-              const int64_t r = (int64_t)m * w;
-              O.d[base + r] = dn;
-              outp[r] = s_x[(m - n0) % RX][tid + 1] + dn;
+              const int64_t r = sid(m);
+              O.d[r] = dn;
+              O.out[(ov && r >= L.Np) ? 3 * r : r] = s_x[(m - n0) % RX][tid + 1] + dn;
             }
         }
     }
@@ -551,38 +554,46 @@ static __global__ void __launch_bounds__(NT) ring_rhs1a_kernel(LatGeom L, RingOp
   const int X0 = O.lo + blockIdx.x * OUTW - HX;
   const int Y0 = O.lo + blockIdx.y * O.rs, Y1 = min(Y0 + O.rs, L.fh - O.lo);
   __syncthreads();
-  if (!ring_cta_fast(L, X0, NT, Y0 - HX, Y1 + 1))
-    {
-      double(&s_ex)[2][4][NT + 2] = *reinterpret_cast<double(*)[2][4][NT + 2]>(raw);
-      ring_rhs1_rows<NT, false>(L, O, s_ex, X0 + tid, Y0, Y1);
-      return;
-    }
+  const bool fast = ring_cta_fast(L, X0, NT, Y0 - HX, Y1 + 1); // else: general index for the addresses, same pipeline
+  const int X = X0 + tid;
+  const bool colok = fast || (X >= 0 && X < L.fw);
   double(&s_x)[2][RX][NT + 2] = *reinterpret_cast<double(*)[2][RX][NT + 2]>(raw); // r1, psi_n: rows n .. n + D
   double(&s_op)[3][RO][NT] = *reinterpret_cast<double(*)[3][RO][NT]>(raw + N_X);  // r2(n - 1), r0(n - 3), dinv(n - 3)
   double(&s_ex)[2][2][NT + 2] = *reinterpret_cast<double(*)[2][2][NT + 2]>(raw + N_X + N_OP); // t(n - 2), hand-over
   const q1::Cst C(L);
-  const bool outcol = tid >= HX && tid < NT - HX;
+  const bool outcol = tid >= HX && tid < NT - HX && (fast || X < L.fw - O.lo);
   const double iml = L.ihx * L.ihy, jxw = 0.25 * L.hx * L.hy;
   const double cm0 = -O.dtth * (1.0 + O.eps), cm2 = -3.0 * O.dtth, cheb0 = O.cheb[0];
-  const int w = L.w, Np = (int)L.Np;
-  const int64_t base = (int64_t)(X0 + tid - L.ex0) - (int64_t)L.ey0 * w; // id of (X, Y) = base + Y w
+  const int w = L.w;
+  const int64_t Np = L.Np;
+  const int64_t base = (int64_t)(X - L.ex0) - (int64_t)L.ey0 * w; // owned node (X, Y): id = base + Y w
+  auto sid = [&](int Y) { return fast ? base + (int64_t)Y * w : (int64_t)lat_id(L, X, Y); };             // scalar field
+  auto vid = [&](int Y, int c) { return fast ? c * Np + base + (int64_t)Y * w : ring_vaddr(L, X, Y, c); }; // 3-vector
   const int n0 = Y0 - HX, nl1 = Y1 + 1, n1 = Y1 + 2;
   auto issue = [&](int n) {
     const int sx = (n - n0) % RX, so = (n - n0) % RO;
     if (n <= nl1)
       {
-        const int64_t r = base + (int64_t)n * w;
-        cp_async8(&s_x[0][sx][tid + 1], O.in + Np + r);
-        cp_async8(&s_x[1][sx][tid + 1], O.psi + r);
+        if (colok)
+          {
+            cp_async8(&s_x[0][sx][tid + 1], O.in + vid(n, 1));
+            cp_async8(&s_x[1][sx][tid + 1], O.psi + vid(n, 0));
+          }
+        else
+          s_x[0][sx][tid + 1] = s_x[1][sx][tid + 1] = 0.0;
       }
     if (n - 1 >= n0 && n - 1 <= nl1 - 1)
-      cp_async8(&s_op[0][so][tid], O.in + 2 * (int64_t)Np + base + (int64_t)(n - 1) * w);
+      {
+        if (colok)
+          cp_async8(&s_op[0][so][tid], O.in + vid(n - 1, 2));
+        else
+          s_op[0][so][tid] = 0.0;
+      }
     const int m = n - 3;
     if (outcol && m >= Y0 && m < Y1)
       {
-        const int64_t r = base + (int64_t)m * w;
-        cp_async8(&s_op[1][so][tid], O.in + r);
-        cp_async8(&s_op[2][so][tid], O.dinv + r);
+        cp_async8(&s_op[1][so][tid], O.in + vid(m, 0));
+        cp_async8(&s_op[2][so][tid], O.dinv + sid(m));
       }
     cp_async_commit();
   };
@@ -647,7 +658,7 @@ static __global__ void __launch_bounds__(NT) ring_rhs1a_kernel(LatGeom L, RingOp
             {
               const double rhs = s_op[1][so][tid] - jxw * Vuse - Dt;
               const double x0 = cheb0 * s_op[2][so][tid] * rhs;
-              const int64_t r = base + (int64_t)m * w;
+              const int64_t r = sid(m);
               O.out[r] = rhs;
               O.d[r] = x0;
               O.out2[r] = x0;
@@ -671,30 +682,39 @@ static __global__ void __launch_bounds__(NT) ring_back1a_kernel(LatGeom L, RingO
   const int X0 = O.lo + blockIdx.x * OUTW - HX;
   const int Y0 = O.lo + blockIdx.y * O.rs, Y1 = min(Y0 + O.rs, L.fh - O.lo);
   __syncthreads();
-  if (!ring_cta_fast(L, X0, NT, Y0 - HX, Y1 - 1 + HX + 1))
-    {
-      double(&s_ex)[2][2][NT + 2] = *reinterpret_cast<double(*)[2][2][NT + 2]>(raw);
-      ring_back1_rows<NT, 1, false>(L, O, s_ex, X0 + tid, Y0, Y1);
-      return;
-    }
+  const bool fast = ring_cta_fast(L, X0, NT, Y0 - HX, Y1 - 1 + HX + 1); // else: general index for the addresses only
+  const int X = X0 + tid;
+  const bool colok = fast || (X >= 0 && X < L.fw);
   double(&s_x)[RX][NT + 2] = *reinterpret_cast<double(*)[RX][NT + 2]>(raw);       // psi (component 0 of z): rows n .. n + D
   double(&s_op)[2][RO][NT] = *reinterpret_cast<double(*)[2][RO][NT]>(raw + N_X);  // r1(n - 1), r2(n - 3)
   double(&s_ex)[2][NT + 2] = *reinterpret_cast<double(*)[2][NT + 2]>(raw + N_X + N_OP); // chi(n - 2)
   const q1::Cst C(L);
-  const bool outcol = tid >= HX && tid < NT - HX;
+  const bool outcol = tid >= HX && tid < NT - HX && (fast || X < L.fw - O.lo);
   const double iml = L.ihx * L.ihy;
-  const int w = L.w, Np = (int)L.Np;
-  const int64_t base = (int64_t)(X0 + tid - L.ex0) - (int64_t)L.ey0 * w;
+  const int w = L.w;
+  const int64_t Np = L.Np;
+  const int64_t base = (int64_t)(X - L.ex0) - (int64_t)L.ey0 * w;
+  auto vid = [&](int Y, int c) { return fast ? c * Np + base + (int64_t)Y * w : ring_vaddr(L, X, Y, c); }; // 3-vector
   const int n0 = Y0 - HX, nx1 = Y1 - 1 + HX, n1 = nx1 + 1;
   auto issue = [&](int n) {
     const int sx = (n - n0) % RX, so = (n - n0) % RO;
     if (n <= nx1)
-      cp_async8(&s_x[sx][tid + 1], O.z + base + (int64_t)n * w);
+      {
+        if (colok)
+          cp_async8(&s_x[sx][tid + 1], O.z + vid(n, 0));
+        else
+          s_x[sx][tid + 1] = 0.0;
+      }
     if (n - 1 >= n0 && n <= n1)
-      cp_async8(&s_op[0][so][tid], O.in + Np + base + (int64_t)(n - 1) * w);
+      {
+        if (colok)
+          cp_async8(&s_op[0][so][tid], O.in + vid(n - 1, 1));
+        else
+          s_op[0][so][tid] = 0.0;
+      }
     const int m = n - 3;
     if (outcol && m >= Y0 && m < Y1)
-      cp_async8(&s_op[1][so][tid], O.in + 2 * (int64_t)Np + base + (int64_t)m * w);
+      cp_async8(&s_op[1][so][tid], O.in + vid(m, 2));
     cp_async_commit();
   };
 #pragma unroll
@@ -724,11 +744,11 @@ static __global__ void __launch_bounds__(NT) ring_back1a_kernel(LatGeom L, RingO
           q1::ysum<false>(C, j, w1k, w1m, Kv, Mv);
           a1 = (mc >= n0) ? iml * (s_op[0][so][tid] - Kv) : 0.0;
           if (outcol && mc >= Y0 && mc < Y1)
-            O.z[Np + base + (int64_t)mc * w] = a1;
+            O.z[vid(mc, 1)] = a1;
           if (outcol && m >= Y0 && m < Y1)
             {
               q1::ysum<false>(C, j, w2k, w2m, Kv, Mv);
-              O.z[2 * (int64_t)Np + base + (int64_t)m * w] = iml * (s_op[1][so][tid] - Kv);
+              O.z[vid(m, 2)] = iml * (s_op[1][so][tid] - Kv);
             }
         }
     }
