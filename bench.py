@@ -280,14 +280,14 @@ def kernel_legs(solver, stats, sweeps, precond, mf, peak, n_nodes, ms_per_step):
         ms, by = pc["ms"], pc["bytes"]
         if mf:
             q1 = ms[3] == 0.0  # Q1: closed-form kernels (csrc/pfc_ring_q1.cuh), the t kernel is fused into the right-hand side
-            add("Chebyshev sweep on the Schur complement: " + ("ring_sweep1_kernel" if q1 else "ring_sweep_kernel"), ms[1], by[0],
+            add("Chebyshev sweep on the Schur complement: " + ("ring_sweep1a_kernel" if q1 else "ring_sweep_kernel"), ms[1], by[0],
                 n_pc * (sweeps - 1))
             if q1:
-                add("t kernel + Schur right-hand side + first Chebyshev step: ring_rhs1_kernel", ms[2], by[1], n_pc)
+                add("t kernel + Schur right-hand side + first Chebyshev step: ring_rhs1a_kernel", ms[2], by[1], n_pc)
             else:
                 add("Schur right-hand side + first Chebyshev step: lat_kernel<LAT_S>", ms[2], by[1], n_pc)
                 add("t = M_L^-1 (r2 - K M_L^-1 r1): ring_t_kernel", ms[3], by[2], n_pc)
-            add("back substitution chi, phi: " + ("ring_back1_kernel" if q1 else "ring_back_kernel"), ms[4], by[3], n_pc)
+            add("back substitution chi, phi: " + ("ring_back1a_kernel" if q1 else "ring_back_kernel"), ms[4], by[3], n_pc)
         else:
             add("K product: kmv_kernel", ms[1], by[0], n_pc * (2 * sweeps + 1))
             add("Schur row: bcd_kernel", ms[2], by[1], n_pc * sweeps)
