@@ -174,6 +174,18 @@ int pfc_get_state_owned(pfc_handle *h, double *Psi_n, double *Psi_n_1);       /*
 /* ---- the hot path ---------------------------------------------------------------------- */
 int pfc_assemble(pfc_handle *h);                        /* assemble_system, mpi.cpp:300-467 [collective] */
 int pfc_residual_norm(pfc_handle *h, double *norm);     /* system_rhs.l2_norm(), mpi.cpp:584 [collective] */
+/* NO COUNTERPART IN THE REFERENCE; added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it).  out_dev[0] = sum_i x_dev[i] * y_dev[i] (x_dev == y_dev:
+ * the squared l2 norm that pfc_residual_norm takes the root of) for n doubles in DEVICE memory, result to DEVICE memory, on
+ * `stream` (a cudaStream_t; NULL = the handle's stream); rank-local, no collective.  Allocates nothing: the partial sums
+ * and the block counter of the reduction live in a file-scope static __device__ array (csrc/pfc_noalloc.cu, 64 KiB + 256 B
+ * on every GPU that loads the library, until exit), which bounds the length: n > PFC_NOALLOC_MAX_N returns
+ * PFC_ERR_BAD_ARGUMENT with a message.  The result does not depend on the SM count (fixed chunk per block, fixed summation
+ * order).  All calls share the scratch: calls that OVERLAP on the GPU (different streams, concurrently replayed graphs)
+ * race; calls on one stream are ordered.  The first call on a device resolves the array's address (cudaGetSymbolAddress,
+ * no allocation): make one call, e.g. with n = 0, before starting a capture. */
+#define PFC_NOALLOC_MAX_N 134217728LL
+int pfc_dot_noalloc(pfc_handle *h, const double *x_dev, const double *y_dev, int64_t n, double *out_dev, void *stream);
 int pfc_solve_update(pfc_handle *h, int64_t *gmres_iters, double *final_residual);
                                                         /* solve_and_update_no_precondition, mpi.cpp:471-492 [collective] */
 int pfc_step(pfc_handle *h, pfc_step_stats *stats);     /* iterate_timestep, mpi.cpp:576-593 [collective] */

@@ -30,6 +30,7 @@ PLAN_LATTICE, PLAN_SKIP_TABLES = 1, 2
 ORTHO_CGS, ORTHO_CGS2, ORTHO_MGS = 0, 1, 2
 PRECOND_NONE, PRECOND_BLOCK_SCHUR = 0, 1
 MAX_NEWTON_RECORD = 256
+NOALLOC_MAX_N = 134217728  # PFC_NOALLOC_MAX_N of include/pfc_b200.h
 
 # lattice constant a = 4 pi / sqrt(3) (src/phase_field_functions/hexagonal_lattice.hpp:35)
 LATTICE_A = 4.0 * np.pi / np.sqrt(3.0)
@@ -110,7 +111,7 @@ class RingView(C.Structure):
 EXPORTED_SYMBOLS = [
     "pfc_default_params", "pfc_create", "pfc_destroy", "pfc_last_error", "pfc_version", "pfc_setup",
     "pfc_nccl_unique_id", "pfc_comm_init", "pfc_comm_mode", "pfc_time_comm", "pfc_set_state", "pfc_get_state", "pfc_n_owned_nodes", "pfc_set_state_owned", "pfc_get_state_owned", "pfc_assemble",
-    "pfc_residual_norm", "pfc_solve_update", "pfc_step", "pfc_run", "pfc_get_rhs", "pfc_get_nnz",
+    "pfc_residual_norm", "pfc_dot_noalloc", "pfc_solve_update", "pfc_step", "pfc_run", "pfc_get_rhs", "pfc_get_nnz",
     "pfc_get_pattern", "pfc_get_matrix_values", "pfc_apply_operator", "pfc_get_dof_permutation",
     "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_selfcheck", "pfc_selfcheck_smoother", "pfc_selfcheck_q1", "pfc_stress", "pfc_stress_owned", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
     "pfc_standin_create_ex", "pfc_standin_destroy",
@@ -170,6 +171,7 @@ def lib():
     L.pfc_get_state.argtypes = [hp, _f64p, _f64p]
     L.pfc_assemble.argtypes = [hp]
     L.pfc_residual_norm.argtypes = [hp, _f64p]
+    L.pfc_dot_noalloc.argtypes = [hp, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
     L.pfc_solve_update.argtypes = [hp, _i64p, _f64p]
     L.pfc_step.argtypes = [hp, C.POINTER(StepStats)]
     L.pfc_run.argtypes = [hp, C.c_int32, C.POINTER(StepStats), _f64p]
@@ -501,6 +503,10 @@ class Solver:
         v = C.c_double()
         self._check(lib().pfc_residual_norm(self._h, C.byref(v)))
         return v.value
+
+    def dot_noalloc(self, x_ptr, y_ptr, n, out_ptr, stream=None):
+        """pfc_dot_noalloc: device pointers (ints), nothing allocated; out_ptr[0] = x . y over n doubles"""
+        self._check(lib().pfc_dot_noalloc(self._h, C.c_void_p(x_ptr), C.c_void_p(y_ptr), n, C.c_void_p(out_ptr), C.c_void_p(stream)))
 
     def solve_update(self):
         its, res = C.c_int64(), C.c_double()
