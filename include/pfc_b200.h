@@ -54,8 +54,16 @@ enum
 enum
 {
   PFC_PRECOND_NONE = 0,        /* mpi.cpp:482 PreconditionIdentity (the reference's active path) */
-  PFC_PRECOND_BLOCK_SCHUR = 1  /* right preconditioner: lumped-mass block elimination + Chebyshev on
+  PFC_PRECOND_BLOCK_SCHUR = 1, /* right preconditioner: lumped-mass block elimination + Chebyshev on
                                   the psi Schur complement (cf. mpi.cpp:496-572, serial.cpp:319-369) */
+  PFC_PRECOND_SCHUR_REDUCED = 2 /* the psi-only Schur-reduced solve of the serial class (serial.cpp:319-369:
+                                  S = B + (D M^-1 K - C) M^-1 K, GMRES on vectors of N instead of 3 N, back substitution
+                                  for chi, phi) without inner mass solves: with dpsi = M^2 y the operator is
+                                  T = B M^2 + D K^2 - C K M (K, M commute on the uniform periodic Q1 lattice), right
+                                  preconditioned by Chebyshev sweeps on the constant-coefficient Schur stand-in.  Same
+                                  tolerance on the residual of the 3-block system.  Q1 + PFC_OPERATOR_MATRIX_FREE on a
+                                  lattice mesh; anywhere else it acts as PFC_PRECOND_BLOCK_SCHUR (pfc_operator_info
+                                  says so) */
 };
 
 /* Constructor arguments of the hot path: the subset of the 15-argument constructor

@@ -28,7 +28,7 @@ PFC_ERR_STATE = 8
 OPERATOR_ASSEMBLED, OPERATOR_MATRIX_FREE, OPERATOR_MATRIX_FREE_GENERAL = 0, 1, 2
 PLAN_LATTICE, PLAN_SKIP_TABLES = 1, 2
 ORTHO_CGS, ORTHO_CGS2, ORTHO_MGS = 0, 1, 2
-PRECOND_NONE, PRECOND_BLOCK_SCHUR = 0, 1
+PRECOND_NONE, PRECOND_BLOCK_SCHUR, PRECOND_SCHUR_REDUCED = 0, 1, 2
 MAX_NEWTON_RECORD = 256
 NOALLOC_MAX_N = 134217728  # PFC_NOALLOC_MAX_N of include/pfc_b200.h
 

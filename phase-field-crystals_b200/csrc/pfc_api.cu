@@ -78,7 +78,9 @@ extern "C" int pfc_create(const pfc_params *p, pfc_handle **out)
     }
   if ((p->operator_kind != PFC_OPERATOR_ASSEMBLED && p->operator_kind != PFC_OPERATOR_MATRIX_FREE &&
        p->operator_kind != PFC_OPERATOR_MATRIX_FREE_GENERAL) ||
-      (p->preconditioner != PFC_PRECOND_NONE && p->preconditioner != PFC_PRECOND_BLOCK_SCHUR) || p->precond_sweeps > 16)
+      (p->preconditioner != PFC_PRECOND_NONE && p->preconditioner != PFC_PRECOND_BLOCK_SCHUR &&
+       p->preconditioner != PFC_PRECOND_SCHUR_REDUCED) ||
+      p->precond_sweeps > 16)
     {
       g_create_error = "operator_kind / preconditioner not available in this build";
       return PFC_ERR_UNSUPPORTED;
@@ -100,6 +102,16 @@ extern "C" int pfc_create(const pfc_params *p, pfc_handle **out)
   // against 237 ms per step at 3 or 5, profiles/r02r), Q2 6 (M2: 24.7 against 25.5 ms at 5, profiles/r02x); assembled: 3 / 5
   h->sweeps = p->precond_sweeps > 0 ? p->precond_sweeps
                                     : (p->operator_kind == PFC_OPERATOR_MATRIX_FREE ? (p->degree == 2 ? 6 : 4) : (p->degree == 2 ? 5 : 3));
+  // The reduced solve shares buffers, ring and fall-back with the block-Schur preconditioner: from here on it is that
+  // preconditioner plus a flag (pfc_setup decides whether the mesh allows it).  Its S~ is well conditioned after the
+  // Jacobi scaling (spectrum about [0.6, 2.5]): two Chebyshev steps do what four do (tests/study_reduced.py)
+  h->want_reduced = p->preconditioner == PFC_PRECOND_SCHUR_REDUCED;
+  if (h->want_reduced)
+    {
+      h->prm.preconditioner = PFC_PRECOND_BLOCK_SCHUR;
+      if (p->precond_sweeps <= 0 && p->operator_kind == PFC_OPERATOR_MATRIX_FREE && p->degree == 1)
+        h->sweeps = 2;
+    }
   int dev = p->device;
   if (dev < 0)
     cudaGetDevice(&dev);
@@ -150,6 +162,7 @@ extern "C" void pfc_destroy(pfc_handle *h)
 }
 
 int launch_assembly(pfc_handle *h, bool const_pass); // pfc_solver.cu
+int reduced_setup(pfc_handle *h);                     // pfc_reduced.cu
 int precond_after_setup(pfc_handle *h);               // pfc_solver.cu
 
 extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
@@ -340,6 +353,22 @@ extern "C" int pfc_setup(pfc_handle *h, const pfc_mesh *mesh)
           h->is_setup = false;
           return rc;
         }
+    }
+  h->reduced = false;
+  if (h->want_reduced)
+    {
+      if (h->lat && P.degree == 1 && h->q1_fast)
+        {
+          rc = reduced_setup(h);
+          if (rc != PFC_OK)
+            {
+              h->is_setup = false;
+              return rc;
+            }
+        }
+      else
+        h->operator_note += std::string(h->operator_note.empty() ? "" : "; ") +
+                            "PFC_PRECOND_SCHUR_REDUCED needs the Q1 lattice path: using PFC_PRECOND_BLOCK_SCHUR";
     }
   PFC_CUDA(h, cudaStreamSynchronize(s));
   return PFC_OK;

@@ -130,10 +130,20 @@ struct pfc_handle
   bool eig_valid = false;
   int solves_since_eig = 0;
 
+  // psi-only reduced solve (PFC_PRECOND_SCHUR_REDUCED, pfc_reduced.cu): active on the Q1 lattice path
+  bool want_reduced = false, reduced = false;
+  pfc::DevBuf<double> d_dinvS, d_cheb_red; // 1 / diag(S~) as a field [owned | ring]; Chebyshev coefficients
+  double *red_y = nullptr, *red_u = nullptr, *red_f = nullptr, *red_z = nullptr; // scalar work fields inside d_pw
+  double *red_xa = nullptr, *red_xb = nullptr, *red_d = nullptr, *red_um = nullptr, *red_wm = nullptr;
+  bool red_have_uw = false; // this solve carries u = M^-1 G, w = M^-1 (K u - H)
+  double red_aux2 = 0;      // squared residual the reduced solve leaves in rows 1, 2 of the 3-block system
+  int64_t red_mass_iters = 0;
+
   // lattice matrix-free path (pfc_lattice.cu): active when operator_kind = PFC_OPERATOR_MATRIX_FREE and the plan found
   // the uniform periodic tensor lattice
   bool lat = false;
   bool q1_fast = true;          // Q1: closed-form kernels of pfc_ring_q1.cuh; off: PFC_Q1_CLOSED_FORM=0 / self-check
+  int j1_variant = 35;          // Q1 J apply kernel and tiling (lat_launch, pfc_lattice.cu); PFC_J1_VARIANT at pfc_setup
   bool lat_k_by_cells = false; // K product by the cell-quadrature kernel instead of the node stencil (self-check)
   pfc::LatGeom lat_geom;
 

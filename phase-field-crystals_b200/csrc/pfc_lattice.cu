@@ -10,6 +10,7 @@
 #include "pfc_lattice.cuh"
 #include "pfc_ring.cuh"
 #include "pfc_ring_q1.cuh"
+#include "pfc_reduced.cuh"
 
 namespace pfc
 {
@@ -111,15 +112,22 @@ int lat_launch(pfc_handle *h, int mode, const LatOp &op, const Ctl *ctl)
     case LAT_J:
       if (q1 && h->q1_fast)
         { // closed-form Q1 algebra, constant blocks as stencils, cp.async pipeline over a tile row (pfc_ring_q1.cuh)
-          static const int variant = getenv("PFC_J1_VARIANT") ? atoi(getenv("PFC_J1_VARIANT")) : 6; // tuning aid
+          const int variant = h->j1_variant; // PFC_J1_VARIANT at pfc_setup (tuning aid)
           const LatGeom &G = h->lat_geom;
-#define PFC_J1(CX, CY, NTILE, MINB)                                                                               \
+#define PFC_J1(CX, CY, NTILE, MINB, ...)                                                                          \
   {                                                                                                           \
     const int ntx = (G.ncx + CX - 2) / (CX - 1), nty = (G.ncy + CY - 2) / (CY - 1);                           \
-    lat_j1_kernel<CX, CY, NTILE, MINB><<<dim3((ntx + NTILE - 1) / NTILE, nty), CX * CY, 0, h->stream>>>(G, op, ctl); \
+    lat_j1_kernel<CX, CY, NTILE, MINB, ##__VA_ARGS__><<<dim3((ntx + NTILE - 1) / NTILE, nty), CX * CY, 0, h->stream>>>(G, op, ctl); \
   }
           switch (variant)
             {
+            case 36: PFC_J1(32, 8, 4, 3, true) break;
+            case 37: PFC_J1(32, 8, 16, 3, true) break;
+            case 38: PFC_J1(32, 6, 8, 4, true) break;
+            case 30: PFC_J1(32, 4, 8, 6, true) break;
+            case 33: PFC_J1(32, 4, 8, 7, true) break;
+            case 34: PFC_J1(32, 8, 8, 4, true) break;
+            case 35: PFC_J1(32, 8, 8, 3, true) break;
             case 0: PFC_J1(16, 16, 1, 4) break;
             case 2: PFC_J1(16, 16, 8, 2) break;
             case 3: PFC_J1(32, 8, 4, 3) break;
@@ -133,13 +141,35 @@ int lat_launch(pfc_handle *h, int mode, const LatOp &op, const Ctl *ctl)
             case 11: PFC_J1(32, 4, 4, 6) break;
             case 12: PFC_J1(32, 8, 8, 3) break;
             case 13: PFC_J1(64, 4, 8, 3) break;
-            default: PFC_J1(32, 4, 8, 6) break; // measured best on B200 (profiles/r02k_j1_tuning.log)
+            case 6: PFC_J1(32, 4, 8, 6) break; // best with the packed node phase (profiles/r02k_j1_tuning.log): 413 us on M4
+            default: PFC_J1(32, 8, 8, 3, true) break; // 35: measured best on B200 (profiles/r04c_j1_rowmap.log, r04e_*): 378 us
             }
 #undef PFC_J1
           h->launches++;
           return PFC_OK;
         }
       return q1 ? launch_mode<1, LAT_J>(h, op, ctl) : launch_mode<2, LAT_J>(h, op, ctl);
+    case LAT_J0:
+      {
+        if (!(q1 && h->q1_fast))
+          return h->fail(PFC_ERR_UNSUPPORTED, "LAT_J0 is a Q1 closed-form kernel");
+        const LatGeom &G = h->lat_geom;
+        constexpr int CX = 32, CY = 8, NTILE = 8;
+        const int ntx = (G.ncx + CX - 2) / (CX - 1), nty = (G.ncy + CY - 2) / (CY - 1);
+        lat_j1_kernel<CX, CY, NTILE, 3, true, true><<<dim3((ntx + NTILE - 1) / NTILE, nty), CX * CY, 0, h->stream>>>(G, op, ctl);
+        h->launches++;
+        return PFC_OK;
+      }
+    case LAT_P:
+      {
+        if (!q1)
+          return h->fail(PFC_ERR_UNSUPPORTED, "LAT_P is a Q1 kernel");
+        const LatGeom &G = h->lat_geom;
+        constexpr int TX = 64, TY = 16;
+        lat_pstage_kernel<TX, TY, 256><<<dim3((G.w + 2 + TX - 1) / TX, (G.h + 2 + TY - 1) / TY), 256, 0, h->stream>>>(G, op, ctl);
+        h->launches++;
+        return PFC_OK;
+      }
     case LAT_S: return q1 ? launch_mode<1, LAT_S>(h, op, ctl) : launch_mode<2, LAT_S>(h, op, ctl);
     case LAT_K: return q1 ? launch_mode<1, LAT_K>(h, op, ctl) : launch_mode<2, LAT_K>(h, op, ctl);
     case LAT_R: return q1 ? launch_mode<1, LAT_R>(h, op, ctl) : launch_mode<2, LAT_R>(h, op, ctl);
@@ -294,6 +324,8 @@ double lat_bytes(const pfc_handle *h, int mode)
     case RING_SWEEP: return 48.0 * N; // x, rhs, dinv, d in, d, x out
     case RING_BACK: return 40.0 * N;  // psi, r1, r2 in, chi, phi out
     case RING_RHS1: return 64.0 * N;  // r0, r1, r2, psi, dinv in, rhs, d, x out (t kernel fused, Q1)
+    case LAT_J0: return 48.0 * N;     // three fields 24 + psi, chi 16 + out 8
+    case LAT_P: return 32.0 * N;      // z in, three fields out
     case RING_RHS: return 72.0 * N;   // m1, t, psi, chi, r0, dinv in, rhs, d, x out
     default: return (h->prm.theta == 1.0 ? 32.0 : 48.0) * N + 32.0 * N; // state in, rhs + 1/diag(B) out
     }
@@ -367,6 +399,7 @@ int lat_setup(pfc_handle *h)
   cudaStream_t s = h->stream;
   LatGeom &G = h->lat_geom;
   h->q1_fast = !(getenv("PFC_Q1_CLOSED_FORM") && atoi(getenv("PFC_Q1_CLOSED_FORM")) == 0); // tuning / A-B aid
+  h->j1_variant = getenv("PFC_J1_VARIANT") ? atoi(getenv("PFC_J1_VARIANT")) : 35;              // tuning / A-B aid
   G.ncx = R.ncx;
   G.ncy = R.ncy;
   G.ex0 = R.ex0;

@@ -29,7 +29,9 @@ enum
              // (stress_calculator_mpi.cpp:204-314)
   LAT_M = 5, // out[c zstride + r] = (M s0[c zstride + .])_r for the fields of zmask: consistent mass matrix as a
              // node stencil (stress_calculator_mpi.cpp:141-200)
-  RING_T = 6, RING_SWEEP = 7, RING_BACK = 8, RING_RHS = 9, RING_RHS1 = 10 // legs of the ring path (lat_bytes)
+  RING_T = 6, RING_SWEEP = 7, RING_BACK = 8, RING_RHS = 9, RING_RHS1 = 10, // legs of the ring path (lat_bytes)
+  LAT_J0 = 11, // out3[r] = (J x)_psi only, out3 a scalar field (Q1 closed form; operator of the reduced solve, pfc_reduced.cuh)
+  LAT_P = 12   // out3 = (M^2 s0, -K M s0, K^2 s0) on the owned nodes and one node beyond (pfc_reduced.cuh)
 };
 
 struct LatOp

@@ -762,7 +762,12 @@ static __global__ void __launch_bounds__(NT) ring_back1a_kernel(LatGeom L, RingO
 // the other resident CTAs (measured: 522 -> 510 us), so a CTA walks over NTILE tiles of a tile row and stages the
 // nodal values of the next tile with cp.async (LDGSTS, 8 bytes: a tile row starts at any node) while it works on the
 // current one; two shared-memory buffers.  NTILE = 1: plain version, no pipeline.
-template <int CX, int CY, int NTILE, int MINB>
+// ROWMAP: the node phase maps thread (cx, cy) of the cell phase to tile node (cx + 1, cy + 1) (the last thread column and
+// row idle) instead of packing the (CX-1) x (CY-1) nodes into the first threads: a warp then reads one shared-memory row
+// with consecutive lanes (no bank conflict where the packed rows of CX - 1 wrap inside a warp).
+// ROW0: only the first block row, out3[r] = B z_psi + C z_chi + D z_phi (the operator of the reduced solve, pfc_reduced.cuh:
+// its input makes the other two rows vanish); out3 is then a scalar field.
+template <int CX, int CY, int NTILE, int MINB, bool ROWMAP = false, bool ROW0 = false>
 static __global__ void __launch_bounds__(CX *CY, MINB) lat_j1_kernel(LatGeom L, LatOp O, const Ctl *ctl)
 {
   if (ctl && ctl->state != 0)
@@ -875,32 +880,38 @@ static __global__ void __launch_bounds__(CX *CY, MINB) lat_j1_kernel(LatGeom L, 
       }
       __syncthreads();
       // ---- nodes of the inner cells: the four corner contributions in a fixed order + the constant 9-point stencils ----
-      if (tid < ONX * ONY)
+      if (ROWMAP ? (tid % CX < ONX && tid / CX < ONY) : tid < ONX * ONY)
         {
-          const int i = 1 + tid % ONX, j = 1 + tid / ONX; // tile node
+          const int i = 1 + (ROWMAP ? tid % CX : tid % ONX), j = 1 + (ROWMAP ? tid / CX : tid / ONX); // tile node
           if (lat_in_window(L, -1, nx0 + i, ny0 + j))
             {
               const double var =
                 (s_c[3][(j - 1) * CX + i - 1] + s_c[2][(j - 1) * CX + i]) + (s_c[1][j * CX + i - 1] + s_c[0][j * CX + i]);
               const q1::Cst C(L);
-              double K0, K1, K2, M1, M2, Mnone;
+              double K0 = 0, K1 = 0, K2, M1 = 0, M2, Mnone;
               double wk[3], wm[3];
+              if (!ROW0)
+                {
 #pragma unroll
-              for (int r = 0; r < 3; ++r)
-                q1::xsum(&S[0][(j - 1 + r) * TNX + i - 1], wk[r], wm[r]);
-              q1::ysum<false>(C, 2, wk, wm, K0, Mnone); // phase 2: slots (0, 1, 2) = (oldest, centre, newest)
+                  for (int r = 0; r < 3; ++r)
+                    q1::xsum(&S[0][(j - 1 + r) * TNX + i - 1], wk[r], wm[r]);
+                  q1::ysum<false>(C, 2, wk, wm, K0, Mnone); // phase 2: slots (0, 1, 2) = (oldest, centre, newest)
 #pragma unroll
-              for (int r = 0; r < 3; ++r)
-                q1::xsum(&S[1][(j - 1 + r) * TNX + i - 1], wk[r], wm[r]);
-              q1::ysum<true>(C, 2, wk, wm, K1, M1);
+                  for (int r = 0; r < 3; ++r)
+                    q1::xsum(&S[1][(j - 1 + r) * TNX + i - 1], wk[r], wm[r]);
+                  q1::ysum<true>(C, 2, wk, wm, K1, M1);
+                }
 #pragma unroll
               for (int r = 0; r < 3; ++r)
                 q1::xsum(&S[2][(j - 1 + r) * TNX + i - 1], wk[r], wm[r]);
               q1::ysum<true>(C, 2, wk, wm, K2, M2);
               const int64_t r = (int64_t)(ny0 + j - L.ey0) * L.w + (nx0 + i - L.ex0); // owned: ly w + lx
               O.out3[r] = fma(0.25 * L.hx * L.hy, var, dtth * fma(-2.0, M2, K2));
-              O.out3[Np + r] = K0 + M1;
-              O.out3[2 * Np + r] = K1 + M2;
+              if (!ROW0)
+                {
+                  O.out3[Np + r] = K0 + M1;
+                  O.out3[2 * Np + r] = K1 + M2;
+                }
             }
         }
       if (k + 1 < nt)

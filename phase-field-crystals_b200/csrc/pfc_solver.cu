@@ -178,6 +178,64 @@ static int apply_operator(pfc_handle *h, double *x, double *y, const Ctl *ctl, b
   return launch_spmv(h, x, y, ctl);
 }
 
+// ---- what a GMRES solve works on ---------------------------------------------------------------------
+// The 3-block Newton system (vectors of 3 Np doubles, operator J, block-Schur right preconditioner), or the psi-only
+// reduced system T y = f of PFC_PRECOND_SCHUR_REDUCED (pfc_reduced.cu: scalar fields of Np doubles, always preconditioned).
+struct KrylovSys
+{
+  bool reduced, precond;
+  int64_t n;  // doubles of the owned part of a vector (even)
+  int64_t st; // doubles between basis vectors
+  double *V, *x, *z, *u;
+  const double *rhs;
+};
+int reduced_apply(pfc_handle *h, double *y, double *out, const pfc::Ctl *ctl, bool halo); // pfc_reduced.cu
+int reduced_precond(pfc_handle *h, double *in, double **out, const pfc::Ctl *ctl);        // pfc_reduced.cu
+int reduced_prepare(pfc_handle *h, double *tol);                                          // pfc_reduced.cu
+int reduced_finish(pfc_handle *h);                                                        // pfc_reduced.cu
+
+static KrylovSys krylov_sys(pfc_handle *h)
+{
+  KrylovSys K;
+  K.reduced = h->reduced;
+  if (h->reduced)
+    {
+      K.precond = true;
+      K.n = h->plan.Np;
+      K.st = h->sstride;
+      K.V = h->d_V.p;
+      K.x = h->red_y;
+      K.z = nullptr; // the preconditioner names its output field
+      K.u = h->red_u;
+      K.rhs = h->red_f;
+    }
+  else
+    {
+      K.precond = h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR;
+      K.n = 3 * h->plan.Np;
+      K.st = h->stride;
+      K.V = h->d_V.p;
+      K.x = h->d_x.p;
+      K.z = h->d_z.p;
+      K.u = h->d_u.p;
+      K.rhs = h->d_rhs.p;
+    }
+  return K;
+}
+// out = A in (halo: refresh the ghosts of `in` first)
+static int sys_apply(pfc_handle *h, const KrylovSys &K, double *in, double *out, const Ctl *ctl, bool halo)
+{
+  return K.reduced ? reduced_apply(h, in, out, ctl, halo) : apply_operator(h, in, out, ctl, halo);
+}
+// *out = field holding P^-1 in
+static int sys_precond(pfc_handle *h, const KrylovSys &K, double *in, double **out, const Ctl *ctl)
+{
+  if (K.reduced)
+    return reduced_precond(h, in, out, ctl);
+  *out = K.z;
+  return precond_apply(h, in, K.z, ctl);
+}
+
 // ---- template dispatch over the Krylov dimension ---------------------------------------------------
 using DotFn = void (*)(const double *, int64_t, const double *, int64_t, double *, double *, unsigned int *, const Ctl *, int, ArDev);
 using AxpyFn = void (*)(const double *, int64_t, double *, int64_t, const double *, const double *, double *, double *, unsigned int *, Ctl *,
@@ -240,18 +298,18 @@ static inline int gs_grid(const pfc_handle *h, int64_t n2, int occ)
 static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0, int i1)
 {
   ensure_tab();
-  const Plan &P = h->plan;
   cudaStream_t s = h->stream;
-  const int64_t n2 = 3 * P.Np / 2;
+  const KrylovSys K = krylov_sys(h);
+  const int64_t n2 = K.n / 2;
   const int grid = vec_grid(h, n2);
   Ctl *ctl = h->d_ctl.p;
   Ctl *gate = h->d_ctl_end.p;
   GmresSmall *g = h->d_small.p;
-  double *V = h->d_V.p;
-  const int64_t st = h->stride;
+  double *V = K.V;
+  const int64_t st = K.st;
   double *partial = h->d_partial.p;
   unsigned int *cnt = h->d_counter.p;
-  const bool precond = h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR;
+  const bool precond = K.precond;
   // peer-memory path: the reduction kernels all-reduce their results in their last block (no collective kernel)
   const ArDev ar = comm_ar_endpoint(h);
   const bool fused = ar.R > 1;
@@ -264,8 +322,8 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0,
     {
       // v0 = b - A x ; rho = ||v0|| ; check ; v0 /= rho          ([dealii-ext] start of the outer loop)
       if (!first_cycle)
-        PFC_TRY(apply_operator(h, h->d_x.p, V, ctl));
-      residual_kernel<<<grid, kVecThreads, 0, s>>>(V, h->d_rhs.p, n2, first_cycle ? 0 : 1, partial, &g->nrm2[0], cnt, ctl, ar);
+        PFC_TRY(sys_apply(h, K, K.x, V, ctl, true));
+      residual_kernel<<<grid, kVecThreads, 0, s>>>(V, K.rhs, n2, first_cycle ? 0 : 1, partial, &g->nrm2[0], cnt, ctl, ar);
       h->launches++;
       if (!fused)
         PFC_TRY(allreduce_sum(h, &g->nrm2[0], 1, ctl));
@@ -279,13 +337,14 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0,
       const int dim = inner + 1;
       double *w = V + (int64_t)dim * st;
       if (precond)
-        { // right preconditioning: w = J P^-1 v_inner
-          PFC_TRY(precond_apply(h, V + (int64_t)inner * st, h->d_z.p, ctl));
-          // lattice path: P^-1 v is already valid one cell beyond the owned nodes (ring overlay), no exchange
-          PFC_TRY(apply_operator(h, h->d_z.p, w, ctl, !h->lat));
+        { // right preconditioning: w = A P^-1 v_inner
+          double *z = nullptr;
+          PFC_TRY(sys_precond(h, K, V + (int64_t)inner * st, &z, ctl));
+          // lattice path: P^-1 v is already valid beyond the owned nodes (ring overlay), no exchange
+          PFC_TRY(sys_apply(h, K, z, w, ctl, !h->lat));
         }
       else
-        PFC_TRY(apply_operator(h, V + (int64_t)inner * st, w, ctl)); // A.vmult
+        PFC_TRY(sys_apply(h, K, V + (int64_t)inner * st, w, ctl, true)); // A.vmult
       g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, st, w, n2, partial, g->dots0, cnt, ctl, 0, ar);
       if (!fused)
         PFC_TRY(allreduce_sum(h, g->dots0, dim + 1, ctl));
@@ -312,14 +371,15 @@ static int enqueue_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0,
   backsolve_kernel<<<1, 1, 0, s>>>(g, ctl, gate, lazy ? 1 : 0);
   if (precond)
     { // x += P^-1 (V y)
-      PFC_CUDA(h, cudaMemsetAsync(h->d_u.p, 0, 3 * P.Np * sizeof(double), s));
-      xupdate_kernel<<<grid, kVecThreads, 0, s>>>(V, st, h->d_u.p, n2, g, ctl, gate);
-      PFC_TRY(precond_apply(h, h->d_u.p, h->d_z.p, gate));
-      axpy1_kernel<<<grid, kVecThreads, 0, s>>>(h->d_x.p, h->d_z.p, 3 * P.Np, gate);
+      PFC_CUDA(h, cudaMemsetAsync(K.u, 0, K.n * sizeof(double), s));
+      xupdate_kernel<<<grid, kVecThreads, 0, s>>>(V, st, K.u, n2, g, ctl, gate);
+      double *z = nullptr;
+      PFC_TRY(sys_precond(h, K, K.u, &z, gate));
+      axpy1_kernel<<<grid, kVecThreads, 0, s>>>(K.x, z, K.n, gate);
       h->launches++;
     }
   else
-    xupdate_kernel<<<grid, kVecThreads, 0, s>>>(V, st, h->d_x.p, n2, g, ctl, gate);
+    xupdate_kernel<<<grid, kVecThreads, 0, s>>>(V, st, K.x, n2, g, ctl, gate);
   h->launches += 3;
   PFC_CUDA(h, cudaMemcpyAsync(h->h_ctl, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s));
   PFC_CUDA(h, cudaGetLastError());
@@ -330,7 +390,7 @@ static int run_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0, int
 {
   if (!h->prm.use_cuda_graph)
     return enqueue_cycle(h, first_cycle, two_pass, i0, i1);
-  const int key = ((i0 * 64 + i1) * 2 + (first_cycle ? 0 : 1)) * 2 + (two_pass ? 1 : 0);
+  const int key = (((i0 * 64 + i1) * 2 + (first_cycle ? 0 : 1)) * 2 + (two_pass ? 1 : 0)) * 2 + (h->reduced ? 1 : 0);
   pfc_handle::CycleGraph &cg = h->cycle_graphs[key];
   if (!cg.exec)
     {
@@ -357,18 +417,19 @@ static int run_cycle(pfc_handle *h, bool first_cycle, bool two_pass, int i0, int
 }
 
 // GMRES as SolverGMRES::solve is used at mpi.cpp:478-482.  x := 0 (mpi.cpp:481).
-static int gmres_solve(pfc_handle *h, int64_t *iters, double *final_res)
+static int gmres_solve(pfc_handle *h, double tol, int64_t *iters, double *final_res)
 {
   const Plan &P = h->plan;
   cudaStream_t s = h->stream;
+  const KrylovSys K = krylov_sys(h);
   Ctl c0;
   std::memset(&c0, 0, sizeof(c0));
-  c0.tol = h->prm.gmres_tol;
+  c0.tol = tol;
   c0.max_iters = h->prm.gmres_max_iters > 0 ? h->prm.gmres_max_iters : P.n_dofs;
   *h->h_ctl = c0;
   PFC_CUDA(h, cudaMemcpyAsync(h->d_ctl.p, h->h_ctl, sizeof(Ctl), cudaMemcpyHostToDevice, s));
   // owned part only: the ghost tail is refreshed before every use
-  PFC_CUDA(h, cudaMemsetAsync(h->d_x.p, 0, 3 * P.Np * sizeof(double), s));
+  PFC_CUDA(h, cudaMemsetAsync(K.x, 0, K.n * sizeof(double), s));
   PFC_CUDA(h, cudaStreamSynchronize(s)); // h_ctl is reused as the read-back buffer
   bool first = true, two_pass = h->prm.orthogonalization == PFC_ORTHO_CGS2;
   // first piece of a cycle: as many iterations as the same solve of the previous time step needed (+ slack, multiple
@@ -462,9 +523,23 @@ extern "C" int pfc_solve_update(pfc_handle *h, int64_t *gmres_iters, double *fin
     return h->fail(PFC_ERR_STATE, "pfc_solve_update before pfc_assemble");
   PFC_CUDA(h, cudaSetDevice(h->device));
   const Plan &P = h->plan;
-  if (h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR)
-    PFC_TRY(precond_refresh(h));
-  PFC_TRY(gmres_solve(h, gmres_iters, final_residual));
+  if (h->reduced)
+    { // psi-only reduced system: right-hand side (and the two mass solves, if the auxiliary residuals are not negligible),
+      // GMRES on scalar fields, then the Newton update from its solution (pfc_reduced.cu)
+      double tol = h->prm.gmres_tol;
+      PFC_TRY(reduced_prepare(h, &tol));
+      double res = 0;
+      PFC_TRY(gmres_solve(h, tol, gmres_iters, &res));
+      if (final_residual)
+        *final_residual = std::sqrt(res * res + h->red_aux2); // of the 3-block system: rows 1, 2 keep their (tiny) residual
+      PFC_TRY(reduced_finish(h));
+    }
+  else
+    {
+      if (h->prm.preconditioner == PFC_PRECOND_BLOCK_SCHUR)
+        PFC_TRY(precond_refresh(h));
+      PFC_TRY(gmres_solve(h, h->prm.gmres_tol, gmres_iters, final_residual));
+    }
   // constraints.distribute(dPsi_n) (mpi.cpp:485); Psi_n += dPsi_n (mpi.cpp:487-491)
   PFC_TRY(halo_exchange(h, h->d_x.p));
   const int64_t nsl = (int64_t)P.slave_id.size();

@@ -239,6 +239,76 @@ def test_matrix_free_step_parity(built, degree, n_refines, n_steps, kind, precon
     s.close()
 
 
+@pytest.mark.parametrize("n_refines,n_steps,dislocations,theta", [(6, 3, True, 1.0), (5, 2, False, 1.0), (7, 2, True, 0.5), (4, 2, True, 1.0)])
+def test_reduced_solve_step_parity(built, n_refines, n_steps, dislocations, theta):
+    """PFC_PRECOND_SCHUR_REDUCED: the psi-only Schur-reduced solve of the serial class (serial.cpp:319-369) with
+    dpsi = M^2 y instead of inner mass solves, against the oracle's 3-block Newton steps.  The initial condition has
+    chi = phi = 0, so the first Newton iteration carries the two mass solves (G, H != 0); later ones do not."""
+    om, st, s, Psi = _setup(built, 1, n_refines, theta=theta, dislocations=dislocations, operator_kind=1, preconditioner=2)
+    kind, note = s.operator_info()
+    assert kind == built.OPERATOR_MATRIX_FREE and "reduced solve active" in note, note
+    s.set_state(Psi, Psi)
+    Pn, Pn1 = Psi.copy(), Psi.copy()
+    for step in range(n_steps):
+        g = s.step()
+        o = om.newton_step(Pn, Pn1, DT, theta, EPS)
+        got = s.get_state()
+        print(f"reduced 2^{n_refines} step {step}: gmres gpu {g['gmres_iters']} oracle {o['gmres_iters']} "
+              f"final residuals {['%.1e' % r for r in g['gmres_final_residual']]} rel {_rel(got, Pn):.2e}")
+        assert g["status"] == 0 and g["n_assemblies"] == o["n_assemblies"]
+        assert all(r <= 1e-10 for r in g["gmres_final_residual"])
+        assert _rel(got[:om.N], Pn[:om.N]) <= 1e-9 and _rel(got, Pn) <= 1e-9
+    s.close()
+
+
+def test_reduced_solve_against_block_schur(built):
+    """Same mesh and steps with the 3-block preconditioned solve and with the reduced one: same states, fewer iterations;
+    and the TRUE residual of the 3-block system for the update the reduced solve returns (J applied to it by
+    pfc_apply_operator) is within the tolerance the reference asks of its GMRES (1e-10 absolute, mpi.cpp:478)."""
+    res = {}
+    for pc in (1, 2):
+        om, st, s, Psi = _setup(built, 1, 6, operator_kind=1, preconditioner=pc)
+        s.set_state(Psi, Psi)
+        its = []
+        for step in range(2):
+            g = s.step()
+            assert g["status"] == 0
+            its.append(g["gmres_iters"])
+        res[pc] = (s.get_state(), its)
+        if pc == 2:
+            X = res[pc][0]
+            free = np.tile(om.master < 0, 3) if om.master.size == om.N else (om.master < 0)
+            for k in range(2):                 # first and second Newton system of the third step
+                s.assemble()
+                rhs = s.get_rhs()
+                n_it, est = s.solve_update()
+                Y = s.get_state()
+                s.set_state(X, res[pc][0])     # J is the Jacobian at the state before the update
+                s.assemble()
+                r = (rhs - s.apply_operator(Y - X))[free]
+                print(f"reduced, Newton system {k}: {n_it} iterations, estimate {est:.2e}, true 3-block residual "
+                      f"{np.linalg.norm(r):.2e}, |rhs| {np.linalg.norm(rhs[free]):.2e}")
+                assert np.linalg.norm(r) <= 2e-10 and est <= 1e-10
+                X = Y
+                s.set_state(X, res[pc][0])
+        s.close()
+    print("gmres iterations block-Schur / reduced:", res[1][1], res[2][1])
+    assert _rel(res[2][0], res[1][0]) <= 1e-9
+    assert sum(sum(i) for i in res[2][1]) < sum(sum(i) for i in res[1][1])
+
+
+def test_reduced_solve_falls_back_off_the_q1_lattice(built):
+    """Q2, or the assembled operator: PFC_PRECOND_SCHUR_REDUCED acts as PFC_PRECOND_BLOCK_SCHUR and says so."""
+    om, st, s, Psi = _setup(built, 2, 4, operator_kind=1, preconditioner=2)
+    kind, note = s.operator_info()
+    assert "using PFC_PRECOND_BLOCK_SCHUR" in note
+    s.set_state(Psi, Psi)
+    g = s.step()
+    o = om.newton_step(Psi.copy(), Psi.copy(), DT, 1.0, EPS)
+    assert g["status"] == 0 and g["n_assemblies"] == o["n_assemblies"]
+    s.close()
+
+
 def test_lattice_and_assembled_preconditioned_runs_agree(built):
     """Same physics, 3 steps, dislocation dipole: lattice matrix-free + block-Schur vs assembled + block-Schur."""
     res = []
