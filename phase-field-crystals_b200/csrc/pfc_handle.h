@@ -135,6 +135,7 @@ struct pfc_handle
   pfc::DevBuf<double> d_dinvS, d_cheb_red; // 1 / diag(S~) as a field [owned | ring]; Chebyshev coefficients
   double *red_y = nullptr, *red_u = nullptr, *red_f = nullptr, *red_z = nullptr; // scalar work fields inside d_pw
   double *red_xa = nullptr, *red_xb = nullptr, *red_d = nullptr, *red_um = nullptr, *red_wm = nullptr;
+  double red_dinvc = 0, red_alpha = 0; // 1 / diag(S~); coefficient of Chebyshev step 0 (x_0 = alpha r)
   bool red_have_uw = false; // this solve carries u = M^-1 G, w = M^-1 (K u - H)
   double red_aux2 = 0;      // squared residual the reduced solve leaves in rows 1, 2 of the 3-block system
   int64_t red_mass_iters = 0;

@@ -277,6 +277,12 @@ static bool ring_deep(bool dflt)
 int ring_launch_t(pfc_handle *h, const RingOp &op, const Ctl *ctl) { PFC_RING_DISPATCH(1, ring_t_kernel, true, false) }
 int ring_launch_sweep(pfc_handle *h, const RingOp &op, const Ctl *ctl)
 {
+  if (op.first)
+    {
+      if (!(h->plan.degree == 1 && h->q1_fast && op.epi == 0))
+        return h->fail(PFC_ERR_UNSUPPORTED, "ring sweep: the first-step form is a Q1 closed-form kernel");
+      return ring_launch<3>(h, op, ctl, ring_sweep1a_kernel<kRingThreads, 4, true>, ring_sweep1a_kernel<kRingThreads, 4, true>);
+    }
   static const int staged = getenv("PFC_SWEEP_STAGED") ? atoi(getenv("PFC_SWEEP_STAGED")) : 4; // 0: off; 3, 4, 6: distance
   if (h->plan.degree == 1 && h->q1_fast && op.epi == 0 && staged > 0) // Chebyshev step: operands staged by cp.async
     {

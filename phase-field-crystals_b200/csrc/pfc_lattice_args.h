@@ -66,6 +66,9 @@ struct RingOp
   const double *psi;         // state Psi_n (3-component vector): coefficient of C from its psi
   double *out2;              // first Chebyshev iterate
   double eps;
+  // reduced solve (pfc_reduced.cuh): first != 0: x_0 = d_0 = alpha rhs is not read but made from rhs, dinv = dinvc
+  int first;
+  double alpha, dinvc;
 };
 int ring_launch_rhs1(pfc_handle *h, const RingOp &op, const Ctl *ctl); // Q1 only
 int ring_launch_t(pfc_handle *h, const RingOp &op, const Ctl *ctl);

@@ -150,6 +150,8 @@ int reduced_setup(pfc_handle *h)
       c[2 * i + 1] = 2.0 * rho_new / delta;
       rho = rho_new;
     }
+  h->red_dinvc = 1.0 / diag;
+  h->red_alpha = c[0] / diag;
   PFC_CUDA(h, h->d_cheb_red.upload(c, s));
   PFC_CUDA(h, cudaStreamSynchronize(s));
   PFC_CUDA(h, cudaGetLastError());
@@ -175,34 +177,52 @@ int reduced_apply(pfc_handle *h, double *y, double *out, const Ctl *ctl, bool ha
 }
 
 // *out = Chebyshev_sweeps(S~) in, valid 3 (sweeps - 1) nodes inside the padded rectangle: one exchange (of `in`), then
-// local kernels on shrinking windows (as precond_apply_ring)
+// local kernels on shrinking windows (as precond_apply_ring).  Step 0 has no stencil (x_0 = d_0 = alpha in): the first
+// sweep makes it on the fly from `in` (ring_sweep1a_kernel<FIRST>), so two steps are ONE pass: in -> out, 16 B per node.
 int reduced_precond(pfc_handle *h, double *in, double **out, const Ctl *ctl)
 {
   const Plan &P = h->plan;
   const int sw = h->sweeps;
   PFC_TRY(halo_exchange_scalar(h, in, ctl));
-  const int64_t n = P.Np + P.n_ghost;
-  cheb0_kernel<<<vgrid(h, n), 256, 0, h->stream>>>(h->red_d, h->red_xa, in, h->d_dinvS.p, h->d_cheb_red.p, n, ctl);
-  h->launches++;
+  if (sw == 1)
+    {
+      const int64_t n = P.Np + P.n_ghost;
+      cheb0_kernel<<<vgrid(h, n), 256, 0, h->stream>>>(h->red_d, h->red_xa, in, h->d_dinvS.p, h->d_cheb_red.p, n, ctl);
+      h->launches++;
+      *out = h->red_xa;
+      PFC_CUDA(h, cudaGetLastError());
+      return PFC_OK;
+    }
   double *x = h->red_xa, *xn = h->red_xb;
   for (int i = 1; i < sw; ++i)
     {
       RingOp o;
       std::memset(&o, 0, sizeof(o));
-      o.x = x;
       o.rhs = in;
-      o.dinv = h->d_dinvS.p;
       o.cheb = h->d_cheb_red.p + 2 * i;
-      o.d = h->red_d;
       o.bbar = 1.0;
       o.dtth = h->prm.dt * h->prm.theta;
       o.lo = 3 * i;
       o.epi = 0;
-      o.out = i == sw - 1 ? h->red_z : xn;
+      if (i == 1)
+        {
+          o.first = 1;
+          o.alpha = h->red_alpha;
+          o.dinvc = h->red_dinvc;
+          o.d = sw > 2 ? h->red_d : nullptr;
+          o.out = sw == 2 ? h->red_z : x;
+        }
+      else
+        {
+          o.x = x;
+          o.dinv = h->d_dinvS.p;
+          o.d = h->red_d;
+          o.out = i == sw - 1 ? h->red_z : xn;
+          std::swap(x, xn);
+        }
       PFC_TRY(ring_launch_sweep(h, o, ctl));
-      std::swap(x, xn);
     }
-  *out = sw > 1 ? h->red_z : h->red_xa;
+  *out = h->red_z;
   PFC_CUDA(h, cudaGetLastError());
   return PFC_OK;
 }

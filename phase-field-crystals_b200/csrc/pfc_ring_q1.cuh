@@ -356,7 +356,10 @@ static __global__ void __launch_bounds__(NT) ring_sweep1_kernel(LatGeom L, RingO
 // scoreboard), one commit group per row; wait_group<D> + the row's __syncthreads make row n visible.  x lands directly
 // in the exchange row its neighbours read.  CTAs on the boundary of the owned rectangle run ring_sweep1_rows.
 // D = prefetch distance in rows; ring depths: x D + 7 (> D + 5: the output row is read again as x_old), operands D + 1
-template <int NT, int D>
+// FIRST (reduced solve, pfc_reduced.cuh): the sweep that follows the stencil-free step 0, x_0 = d_0 = alpha r with the
+// constant Jacobi scaling: only r is staged (as "x"; S~ x_0 = alpha S~ r), nothing else is read, d is written only if
+// another sweep follows (O.d != 0).  Replaces a pass that wrote x_0, d_0 and a sweep that read them back with rhs and dinv.
+template <int NT, int D, bool FIRST = false>
 static __global__ void __launch_bounds__(NT) ring_sweep1a_kernel(LatGeom L, RingOp O, const Ctl *ctl)
 {
   if (ctl && ctl->state != 0)
@@ -392,12 +395,12 @@ static __global__ void __launch_bounds__(NT) ring_sweep1a_kernel(LatGeom L, Ring
     if (n <= nx1)
       {
         if (colok)
-          cp_async8(&s_x[(n - n0) % RX][tid + 1], O.x + xid(n));
+          cp_async8(&s_x[(n - n0) % RX][tid + 1], (FIRST ? O.rhs : O.x) + xid(n));
         else
           s_x[(n - n0) % RX][tid + 1] = 0.0;
       }
     const int m = n - 5;
-    if (outcol && m >= Y0 && m < Y1)
+    if (!FIRST && outcol && m >= Y0 && m < Y1)
       {
         const int so = (n - n0) % RO;
         const int64_t r = sid(m);
@@ -446,11 +449,22 @@ static __global__ void __launch_bounds__(NT) ring_sweep1a_kernel(LatGeom L, Ring
             {
               q1::ysum<true>(C, j, w3k, w3m, Kv, Mv);   // K t2, M t2 at the output row
               const double Sx = O.bbar * Mx_m + O.dtth * fma(-2.0, Mv, Kv);
-              const int so = (n - n0) % RO;
-              const double dn = c0 * s_op[2][so][tid] + c1 * s_op[1][so][tid] * (s_op[0][so][tid] - Sx);
               const int64_t r = sid(m);
-              O.d[r] = dn;
-              O.out[(ov && r >= L.Np) ? 3 * r : r] = s_x[(m - n0) % RX][tid + 1] + dn;
+              if (FIRST)
+                {
+                  const double rm = s_x[(m - n0) % RX][tid + 1], x0 = O.alpha * rm; // x_0 = d_0 = alpha r
+                  const double dn = c0 * x0 + c1 * O.dinvc * (rm - O.alpha * Sx);
+                  if (O.d)
+                    O.d[r] = dn;
+                  O.out[(ov && r >= L.Np) ? 3 * r : r] = x0 + dn;
+                }
+              else
+                {
+                  const int so = (n - n0) % RO;
+                  const double dn = c0 * s_op[2][so][tid] + c1 * s_op[1][so][tid] * (s_op[0][so][tid] - Sx);
+                  O.d[r] = dn;
+                  O.out[(ov && r >= L.Np) ? 3 * r : r] = s_x[(m - n0) % RX][tid + 1] + dn;
+                }
             }
         }
     }
