@@ -271,9 +271,29 @@ def kernel_legs(solver, stats, sweeps, precond, mf, peak, n_nodes, ms_per_step):
         legs[name] = {"ms": ms, "algorithmic_bytes": nbytes, "gbs": nbytes / ms / 1e6, "frac": nbytes / ms / 1e6 / peak,
                       "launches_per_step": per_step, "share_of_step": ms * per_step / ms_per_step}
 
-    ms_op, by_op = solver.time_operator(reps=20)
-    add(("J apply: lat_j1_kernel" if solver.params.degree == 1 else "J apply: lat_kernel<LAT_J>") if mf else "J apply: spmv_sell_kernel",
-        ms_op, by_op, n_it + n_solve)
+    reduced = "reduced solve active" in solver.operator_info()[1]
+    vec = (8.0 if reduced else 24.0) * n_nodes  # bytes of one Krylov vector
+    if reduced:
+        # psi-only reduced solve (csrc/pfc_reduced.cuh): per iteration one operator T y (two kernels) and one preconditioner
+        # application (one exchange + sweeps - 1 sweep kernels); + the x update at the end of every cycle, the start of a
+        # restarted cycle and the Newton update (three fields once per solve)
+        rd = solver.time_reduced(reps=20)
+        ms, by = rd["ms"], rd["bytes"]
+        n_app = n_it + n_solve
+        add("reduced operator, the three fields M^2 y, -K M y, K^2 y: lat_pstage_kernel", ms[1], by[1], n_app + n_solve)
+        add("reduced operator, row 0 of J on the three fields: lat_j1_kernel<ROW0>", ms[2], by[2], n_app)
+        if sweeps >= 2:
+            add("Chebyshev steps 0 and 1 on the Schur stand-in in one pass: ring_sweep1a_kernel<FIRST>", ms[4], by[4], n_app)
+        if sweeps >= 3:
+            add("later Chebyshev sweep: ring_sweep1a_kernel", ms[5], by[5], n_app * (sweeps - 2))
+        legs["reduced operator T y (all its kernels)"] = {"ms": ms[0], "launches_per_step": n_app, "share_of_step": ms[0] * n_app / ms_per_step}
+        legs["reduced preconditioner (exchange + all its kernels)"] = {"ms": ms[3], "launches_per_step": n_app,
+                                                                       "share_of_step": ms[3] * n_app / ms_per_step}
+        precond = False
+    else:
+        ms_op, by_op = solver.time_operator(reps=20)
+        add(("J apply: lat_j1_kernel" if solver.params.degree == 1 else "J apply: lat_kernel<LAT_J>") if mf else "J apply: spmv_sell_kernel",
+            ms_op, by_op, n_it + n_solve)
     if precond:
         pc = solver.time_precond(reps=20)
         n_pc = n_it + n_solve  # one application per iteration + the x update at the end of a cycle
@@ -294,7 +314,6 @@ def kernel_legs(solver, stats, sweeps, precond, mf, peak, n_nodes, ms_per_step):
         legs["preconditioner application (all its kernels)"] = {"ms": pc["ms_apply"], "launches_per_step": n_pc,
                                                                 "share_of_step": pc["ms_apply"] * n_pc / ms_per_step}
     kry = solver.time_krylov(dim=14, reps=10)
-    vec = 24.0 * n_nodes
     dot_bytes = sum((d + 1) * vec for n in its for d in range(1, n + 1)) / K
     axpy_bytes = sum((d + 2) * vec for n in its for d in range(1, n + 1)) / K
     for nm, ms14, b14, tot in (("multidot", kry["ms_dot"], kry["bytes_dot"], dot_bytes), ("multiaxpy", kry["ms_axpy"], kry["bytes_axpy"], axpy_bytes)):
@@ -318,7 +337,9 @@ def main():
     ap.add_argument("--ic", default="", choices=["", "perfect", "dipole", "polycrystal"])
     ap.add_argument("--ortho", type=int, default=0)
     ap.add_argument("--no-graph", action="store_true")
-    ap.add_argument("--precond", type=int, default=1)
+    ap.add_argument("--precond", type=int, default=-1,
+                    help="0 none (reference algorithm), 1 block-Schur right preconditioner, 2 psi-only reduced solve "
+                         "(Q1 matrix-free; elsewhere it acts as 1); default: 2 for Q1 matrix-free workloads, else 1")
     ap.add_argument("--assembled", action="store_true", help="assembled shared-pattern SELL-32 operator instead of matrix-free")
     ap.add_argument("--sweeps", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -365,6 +386,8 @@ def main():
 
     wl = resolve_workload(args)
     degree, n_refines = wl["degree"], wl["n_refines"]
+    if args.precond < 0:
+        args.precond = 2 if (degree == 1 and args.mf) else 1
     S, p1, p2 = box(degree, n_refines)
     A0 = P.default_A0(PSI0, EPS)
     mesh = P.StandIn(degree, n_refines, p1, p2, rank=rank, n_ranks=world)
@@ -382,6 +405,7 @@ def main():
 
     solver = make_solver(1 if args.mf else 0)
     solver.setup(mesh)
+    reduced_active = "reduced solve active" in solver.operator_info()[1]
     Psi0 = initial_condition(mesh, wl, p1, p2, S, A0)
     solver.set_state(Psi0, Psi0)
     n_own = solver.n_owned_nodes()
@@ -499,6 +523,25 @@ def main():
             parity["gmres_iters_1rank_timed_steps"] = its1[args.warmup:]
         parity["ok"] = bool(e_psi <= parity["bar"])
 
+    if world == 1 and reduced_active and not args.no_parity:
+        # the timed (reduced) solve against the 3-block solve with the block-Schur preconditioner: same mesh, initial
+        # condition and steps; both solve every Newton system to 1e-10 on the residual of the 3-block system
+        t0 = time.perf_counter()
+        s3 = P.Solver(degree=degree, dt=DT, theta=THETA, eps=EPS, device=local, orthogonalization=args.ortho,
+                      use_cuda_graph=0 if args.no_graph else 1, preconditioner=1, operator_kind=1)
+        s3.setup(mesh)
+        s3.set_state(Psi0, Psi0)
+        its3 = [s3.step()["gmres_iters_total"] for _ in range(args.warmup + args.steps)]
+        ref3 = s3.get_state_owned()
+        s3.close()
+        d = end_own - ref3
+        parity["reduced_vs_3block_solve"] = {
+            "psi_rel_l2": float(np.linalg.norm(d[:n_own]) / np.linalg.norm(ref3[:n_own])),
+            "all_blocks_rel_l2": float(np.linalg.norm(d) / np.linalg.norm(ref3)), "steps": args.warmup + args.steps,
+            "bar": 1e-9 * (args.warmup + args.steps), "gmres_iters_3block_timed_steps": its3[args.warmup:],
+            "seconds": time.perf_counter() - t0}
+        parity["reduced_vs_3block_solve"]["ok"] = bool(parity["reduced_vs_3block_solve"]["psi_rel_l2"] <= parity["reduced_vs_3block_solve"]["bar"])
+
     # ---- config 5: the other operator path on the same run ----------------------------------------------
     other = None
     if wl.get("both_operators"):
@@ -529,10 +572,12 @@ def main():
     peak, peak_src = measured_peak()
     ms_per_step = ms_dev / args.steps
     sweeps = args.sweeps if args.sweeps > 0 else ((6 if degree == 2 else 4) if args.mf else (5 if degree == 2 else 3))  # the library's defaults
+    if reduced_active and args.sweeps <= 0:
+        sweeps = 2  # the library's default of the reduced solve
     legs = None
     if not args.no_legs:
         solver.assemble()
-        legs = kernel_legs(solver, stats, sweeps, args.precond == 1, args.mf, peak, n_own, ms_per_step)
+        legs = kernel_legs(solver, stats, sweeps, args.precond >= 1, args.mf, peak, n_own, ms_per_step)
     comm_legs = solver.time_comm(reps=50) if world > 1 else None
 
     if rank == 0:
@@ -544,14 +589,18 @@ def main():
             "config": {"workload": workload_string(wl, n_dofs), "n_dofs": int(n_dofs), "baseline_config": wl["config"],
                        "partition": f"{world} contiguous chunk(s) of the Morton curve (p4est), {n_own} owned nodes per component on rank 0",
                        "solver": ("GMRES(28) unpreconditioned, tol 1e-10 abs, Newton tol 1e-8 (reference algorithm)" if args.precond == 0 else
-                                  f"GMRES(28), right block-Schur preconditioner (lumped mass + {sweeps} Jacobi-Chebyshev sweeps), same tol 1e-10 abs on the true residual, Newton tol 1e-8"),
+                                  (f"psi-only Schur-reduced Newton system (serial.cpp:319-369) with dpsi = M^2 y instead of inner mass solves: "
+                                   f"GMRES(28) on vectors of N doubles, right preconditioner = {sweeps} Jacobi-Chebyshev steps on the "
+                                   "constant-coefficient Schur stand-in, same tol 1e-10 abs on the residual of the 3-block system, Newton tol 1e-8"
+                                   if reduced_active else
+                                   f"GMRES(28), right block-Schur preconditioner (lumped mass + {sweeps} Jacobi-Chebyshev sweeps), same tol 1e-10 abs on the true residual, Newton tol 1e-8")),
                        "operator": ("matrix-free, sum-factorised lattice cell kernels (no stored matrix)" if args.mf
                                     else "assembled (shared-pattern SELL-32)"),
                        "orthogonalization": ["CGS+Kelley", "CGS2"][args.ortho],
                        "comm": ["single rank", "NCCL", "peer-memory kernels over NVLink (CUDA IPC) + NCCL bootstrap"][solver.comm_mode()],
                        "cuda_graph": not args.no_graph,
                        "l2": ("timed steps: every GMRES iteration streams the Krylov basis, "
-                              f"{(29 * 24.0 * n_own) / 1e6:.0f} MB per rank against the 126 MB L2, no flush; "
+                              f"{(29 * (8.0 if reduced_active else 24.0) * n_own) / 1e6:.0f} MB per rank against the 126 MB L2, no flush; "
                               "kernel legs: operands rotated through the basis vectors"),
                        "newton_assemblies_per_step": [s["n_assemblies"] for s in stats], "gmres_iters_per_step": its},
             "ms_wall_per_step": ms_wall / args.steps,

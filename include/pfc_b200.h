@@ -220,6 +220,12 @@ int pfc_time_assembly(pfc_handle *h, int32_t reps, double *ms_mean, double *byte
  *                   (lat_kernel<LAT_S>), ms5[3] t kernel (ring_t_kernel), ms5[4] back substitution (ring_back_kernel)
  * bytes4[k] = algorithmic bytes of one launch of leg k + 1 (0 where the leg does not exist) */
 int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms5, double *bytes4);
+/* legs of the reduced solve (PFC_PRECOND_SCHUR_REDUCED active), device time per launch replayed from a CUDA graph:
+ *   ms6[0] operator T y = row 0 of J (M^2 y, -K M y, K^2 y) (both kernels), ms6[1] lat_pstage_kernel (the three fields),
+ *   ms6[2] lat_j1_kernel<ROW0>, ms6[3] preconditioner (one exchange + the Chebyshev sweeps), ms6[4] the first sweep
+ *   (steps 0 and 1 in one pass), ms6[5] a later sweep (0 if precond_sweeps < 3); bytes6[k] = algorithmic bytes of a
+ *   launch of leg k (0 for leg 3).  pfc_time_krylov times the Gram-Schmidt kernels on the reduced vectors then. */
+int pfc_time_reduced(pfc_handle *h, int32_t reps, double *ms6, double *bytes6);
 /* consistency of redundant kernel forms on a deterministic pseudo-random field (lattice path: K product as node
  * stencil vs cell quadrature); max_rel = max |a - b| / max |a|.  0 when the handle has no redundant form. [collective] */
 int pfc_selfcheck(pfc_handle *h, double *max_rel);

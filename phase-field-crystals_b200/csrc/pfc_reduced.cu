@@ -318,3 +318,89 @@ int reduced_finish(pfc_handle *h)
   PFC_CUDA(h, cudaGetLastError());
   return PFC_OK;
 }
+
+// bench.py roofline legs of the reduced solve (include/pfc_b200.h), device time per launch replayed from a CUDA graph,
+// operands rotating through the Krylov basis (scalar fields, sstride apart) so that they do not stay in L2:
+//   0 operator T y (both kernels)   1 lat_pstage_kernel   2 lat_j1_kernel<ROW0>
+//   3 preconditioner (exchange + sweeps)   4 first sweep (ring_sweep1a_kernel<FIRST>)   5 a later sweep (0 if sweeps < 3)
+extern "C" int pfc_time_reduced(pfc_handle *h, int32_t reps, double *ms6, double *bytes6)
+{
+  if (!h || reps < 1 || !ms6)
+    return PFC_ERR_BAD_ARGUMENT;
+  if (!h->is_setup || !h->reduced || !h->has_state)
+    return h->fail(PFC_ERR_STATE, "pfc_time_reduced needs an active reduced solve (PFC_PRECOND_SCHUR_REDUCED on the Q1 lattice path) and a state");
+  PFC_CUDA(h, cudaSetDevice(h->device));
+  cudaStream_t s = h->stream;
+  const int half = std::max(1, h->n_basis / 2), sw = h->sweeps;
+  const double N = (double)h->lat_geom.w * h->lat_geom.h;
+  auto vin = [&](int i) { return h->d_V.p + (int64_t)(i % half) * h->sstride; };
+  auto vout = [&](int i) { return h->d_V.p + (int64_t)(half + i % half) * h->sstride; };
+  for (int leg = 0; leg < 6; ++leg)
+    {
+      ms6[leg] = 0;
+      if (bytes6)
+        bytes6[leg] = 0;
+      if ((leg >= 4 && sw < 2) || (leg == 5 && sw < 3))
+        continue;
+      cudaGraph_t graph = nullptr;
+      cudaGraphExec_t exec = nullptr;
+      const int64_t before = h->launches;
+      PFC_CUDA(h, cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+      int rc = PFC_OK;
+      for (int i = 0; i < reps && rc == PFC_OK; ++i)
+        {
+          double *z = nullptr;
+          RingOp o;
+          std::memset(&o, 0, sizeof(o));
+          o.bbar = 1.0, o.dtth = h->prm.dt * h->prm.theta, o.epi = 0;
+          LatOp a = lat_op(h);
+          switch (leg)
+            {
+            case 0: rc = reduced_apply(h, vin(i), vout(i), nullptr, false); break;
+            case 1: a.s0 = vin(i), a.out3 = h->d_z.p, rc = lat_launch(h, LAT_P, a, nullptr); break;
+            case 2: a.in3a = h->d_V.p + (int64_t)(i % 4) * h->stride, a.in3b = h->d_psi_n.p, a.out3 = vout(i);
+              rc = lat_launch(h, LAT_J0, a, nullptr);
+              break;
+            case 3: rc = reduced_precond(h, vin(i), &z, nullptr); break;
+            case 4:
+              o.rhs = vin(i), o.cheb = h->d_cheb_red.p + 2, o.lo = 3, o.first = 1, o.alpha = h->red_alpha, o.dinvc = h->red_dinvc;
+              o.d = sw > 2 ? h->red_d : nullptr, o.out = vout(i);
+              rc = ring_launch_sweep(h, o, nullptr);
+              break;
+            default:
+              o.x = vin(i), o.rhs = vin(i + 1), o.dinv = h->d_dinvS.p, o.d = h->red_d, o.cheb = h->d_cheb_red.p + 4, o.lo = 6, o.out = vout(i);
+              rc = ring_launch_sweep(h, o, nullptr);
+              break;
+            }
+        }
+      cudaError_t e = cudaStreamEndCapture(s, &graph);
+      h->launches = before;
+      if (rc != PFC_OK)
+        {
+          if (graph)
+            cudaGraphDestroy(graph);
+          return rc;
+        }
+      PFC_CUDA(h, e);
+      PFC_CUDA(h, cudaGraphInstantiate(&exec, graph, 0));
+      cudaGraphDestroy(graph);
+      PFC_CUDA(h, cudaGraphLaunch(exec, s)); // warm-up
+      PFC_CUDA(h, cudaEventRecord(h->ev[0], s));
+      PFC_CUDA(h, cudaGraphLaunch(exec, s));
+      PFC_CUDA(h, cudaEventRecord(h->ev[1], s));
+      PFC_CUDA(h, cudaStreamSynchronize(s));
+      float ms = 0;
+      PFC_CUDA(h, cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]));
+      cudaGraphExecDestroy(exec);
+      ms6[leg] = ms / reps;
+      if (bytes6)
+        {
+          // algorithmic bytes per node: z in + three fields out | three fields + psi, chi in, one out | r in, x out
+          // (+ d out when a sweep follows) | x, rhs, dinv, d in, d, x out
+          const double per_node[6] = {32.0 + 48.0, 32.0, 48.0, 0.0, sw > 2 ? 24.0 : 16.0, 48.0};
+          bytes6[leg] = per_node[leg] * N;
+        }
+    }
+  // the 3-component test operands of leg 2 and the rotation leave the basis dirty; the next solve rebuilds what it reads
+  return PFC_OK;
+}

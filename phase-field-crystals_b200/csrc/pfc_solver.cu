@@ -751,12 +751,11 @@ extern "C" int pfc_time_krylov(pfc_handle *h, int32_t dim, int32_t reps, double 
     return h->fail(PFC_ERR_BAD_ARGUMENT, "dim must be in [1, restart]");
   PFC_CUDA(h, cudaSetDevice(h->device));
   ensure_tab();
-  const Plan &P = h->plan;
   cudaStream_t s = h->stream;
-  const int64_t n2 = 3 * P.Np / 2;
-  const int grid = vec_grid(h, n2);
+  const KrylovSys K = krylov_sys(h); // the vectors of the active solve: 3 Np doubles, or Np (reduced solve)
+  const int64_t n2 = K.n / 2, stride = K.st;
   GmresSmall *g = h->d_small.p;
-  double *V = h->d_V.p, *w = V + (int64_t)dim * h->stride;
+  double *V = K.V, *w = V + (int64_t)dim * stride;
   // neutral control block: state 0, no second pass; coefficients 0 so that w is unchanged
   PFC_CUDA(h, cudaMemsetAsync(h->d_ctl.p, 0, sizeof(Ctl), s));
   PFC_CUDA(h, cudaMemsetAsync(g->dots1, 0, sizeof(g->dots1), s));
@@ -765,15 +764,15 @@ extern "C" int pfc_time_krylov(pfc_handle *h, int32_t dim, int32_t reps, double 
     {
       for (int i = 0; i < 2; ++i) // warm-up
         if (k == 0)
-          g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0, ArDev{});
+          g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0, ArDev{});
         else
-          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, nullptr, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
+          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, stride, w, n2, g->dots1, nullptr, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
       PFC_CUDA(h, cudaEventRecord(h->ev[0], s));
       for (int i = 0; i < reps; ++i)
         if (k == 0)
-          g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0, ArDev{});
+          g_dot[dim]<<<gs_grid(h, n2, g_dot_occ[dim]), kVecThreads, 0, s>>>(V, stride, w, n2, h->d_partial.p, g->dots0, h->d_counter.p, h->d_ctl.p, 0, ArDev{});
         else
-          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, h->stride, w, n2, g->dots1, nullptr, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
+          g_axpy[dim]<<<gs_grid(h, n2, g_axpy_occ[dim]), kVecThreads, 0, s>>>(V, stride, w, n2, g->dots1, nullptr, h->d_partial.p, &g->nrm2[1], h->d_counter.p, h->d_ctl.p, 0, ArDev{});
       h->launches += reps + 2;
       PFC_CUDA(h, cudaEventRecord(h->ev[1], s));
       PFC_CUDA(h, cudaStreamSynchronize(s));
@@ -781,7 +780,7 @@ extern "C" int pfc_time_krylov(pfc_handle *h, int32_t dim, int32_t reps, double 
       (k == 0 ? *ms_dot : *ms_axpy) = ms / reps;
     }
   PFC_CUDA(h, cudaGetLastError());
-  const double vec = 24.0 * (double)P.Np; // one vector of 3 Np doubles
+  const double vec = 8.0 * (double)K.n; // one vector
   if (bytes_dot)
     *bytes_dot = (dim + 1) * vec;
   if (bytes_axpy)

@@ -18,7 +18,9 @@ def _n_gpus():
                                                           (1, 5, 2, '{"preconditioner": 1}'), (2, 4, 1, '{"preconditioner": 1}'),
                                                           (1, 5, 2, '{"operator_kind": 1}'), (2, 4, 2, '{"operator_kind": 1, "preconditioner": 1}'),
                                                           (1, 5, 2, '{"operator_kind": 1, "preconditioner": 1}'),
-                                                          (2, 4, 1, '{"operator_kind": 1, "preconditioner": 1, "check_stress": 1}')])
+                                                          (2, 4, 1, '{"operator_kind": 1, "preconditioner": 1, "check_stress": 1}'),
+                                                          (1, 6, 2, '{"operator_kind": 1, "preconditioner": 2}'),
+                                                          (1, 5, 2, '{"operator_kind": 1, "preconditioner": 2, "theta": 0.5}')])
 @pytest.mark.parametrize("no_p2p", [0, 1])
 def test_ranks_match_oracle(built, degree, n_refines, steps, extra, no_p2p):
     """no_p2p = 0: halo exchange and all-reduce by the peer-memory kernels over NVLink; 1: NCCL."""
@@ -30,7 +32,7 @@ def test_ranks_match_oracle(built, degree, n_refines, steps, extra, no_p2p):
     # 2 ranks for every case; the full box (up to 8 ranks) only for the bench-default configuration over peer memory,
     # so that the suite stays within minutes on an 8-GPU box
     worlds = {2}
-    if '"operator_kind": 1, "preconditioner": 1' in extra and not no_p2p:
+    if ('"operator_kind": 1, "preconditioner": 1' in extra or '"preconditioner": 2}' in extra) and not no_p2p:
         worlds.add(min(n, 8))
     for world in sorted(worlds):
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
