@@ -627,9 +627,9 @@ def main():
                                     "vector kernels, device-side control and (N > 1) halo exchanges"}
             line["step"]["frac"] = line["step"]["algorithmic_gbs"] / peak
             try:  # dram traffic of the roofline kernel from the committed ncu capture of this workload
-                with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
+                with open(os.path.join(ROOT, "profiles", "r04_traffic.json")) as f:
                     tr = json.load(f)
-                ent = tr.get(wl["name"], {}).get(top)
+                ent = tr.get(wl["name"] + ("/reduced" if reduced_active else ""), {}).get(top)
                 if ent and world == 1 and not wl["custom"]:
                     line["roofline"]["traffic"] = ent["bytes_per_launch"]
                     line["roofline"]["traffic_source"] = ent["source"]

@@ -226,6 +226,10 @@ int pfc_time_precond(pfc_handle *h, int32_t reps, double *ms5, double *bytes4);
  *   (steps 0 and 1 in one pass), ms6[5] a later sweep (0 if precond_sweeps < 3); bytes6[k] = algorithmic bytes of a
  *   launch of leg k (0 for leg 3).  pfc_time_krylov times the Gram-Schmidt kernels on the reduced vectors then. */
 int pfc_time_reduced(pfc_handle *h, int32_t reps, double *ms6, double *bytes6);
+/* host only, no GPU: the constant-coefficient Schur stand-in S~ = M + dt theta (K - 2 M)(M_L^-1 K)^2 of the Chebyshev sweeps on
+ * a periodic Q1 lattice of hx x hy cells: out3 = {its diagonal entry, min, max of the spectrum of diag^-1 S~} (what the
+ * reduced solve takes its Jacobi scaling and Chebyshev interval from; checked against assembled matrices on the CPU) */
+int pfc_reduced_symbol(double hx, double hy, double dt_theta, double *out3);
 /* consistency of redundant kernel forms on a deterministic pseudo-random field (lattice path: K product as node
  * stencil vs cell quadrature); max_rel = max |a - b| / max |a|.  0 when the handle has no redundant form. [collective] */
 int pfc_selfcheck(pfc_handle *h, double *max_rel);

@@ -113,7 +113,7 @@ EXPORTED_SYMBOLS = [
     "pfc_nccl_unique_id", "pfc_comm_init", "pfc_comm_mode", "pfc_time_comm", "pfc_set_state", "pfc_get_state", "pfc_n_owned_nodes", "pfc_set_state_owned", "pfc_get_state_owned", "pfc_assemble",
     "pfc_residual_norm", "pfc_dot_noalloc", "pfc_solve_update", "pfc_step", "pfc_run", "pfc_get_rhs", "pfc_get_nnz",
     "pfc_get_pattern", "pfc_get_matrix_values", "pfc_apply_operator", "pfc_get_dof_permutation",
-    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_time_reduced", "pfc_selfcheck", "pfc_selfcheck_smoother", "pfc_selfcheck_q1", "pfc_stress", "pfc_stress_owned", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
+    "pfc_time_operator", "pfc_time_assembly", "pfc_time_krylov", "pfc_time_precond", "pfc_time_reduced", "pfc_reduced_symbol", "pfc_selfcheck", "pfc_selfcheck_smoother", "pfc_selfcheck_q1", "pfc_stress", "pfc_stress_owned", "pfc_vtu_write", "pfc_vtu_piece_name", "pfc_output", "pfc_standin_create",
     "pfc_standin_create_ex", "pfc_standin_destroy",
     "pfc_standin_mesh", "pfc_standin_n_nodes", "pfc_standin_support_points",
     "pfc_standin_hexagonal_lattice", "pfc_standin_polycrystal", "pfc_plan_build", "pfc_plan_build_ex", "pfc_plan_get_lattice", "pfc_plan_ring_overlay", "pfc_plan_get_ring", "pfc_operator_info", "pfc_plan_get_view", "pfc_plan_monolithic",
@@ -221,6 +221,7 @@ def lib():
     L.pfc_plan_get_ring.argtypes = [hp, C.POINTER(RingView)]
     L.pfc_plan_get_ring.restype = None
     L.pfc_time_reduced.argtypes = [hp, C.c_int32, _f64p, _f64p]
+    L.pfc_reduced_symbol.argtypes = [C.c_double, C.c_double, C.c_double, _f64p]
     L.pfc_operator_info.argtypes = [hp, C.c_char_p, C.c_int32]
     L.pfc_plan_get_view.argtypes = [hp, C.POINTER(PlanView)]
     L.pfc_plan_get_view.restype = None
@@ -229,6 +230,15 @@ def lib():
     L.pfc_plan_destroy.restype = None
     _lib = L
     return L
+
+
+def reduced_symbol(hx, hy, dt_theta):
+    """(diag(S~), lambda_min, lambda_max of diag^-1 S~): pfc_reduced_symbol, host only"""
+    out = (C.c_double * 3)()
+    rc = lib().pfc_reduced_symbol(hx, hy, dt_theta, out)
+    if rc != 0:
+        raise ValueError("pfc_reduced_symbol: bad argument")
+    return tuple(out)
 
 
 def _p(a, ct):

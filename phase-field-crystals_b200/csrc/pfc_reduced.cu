@@ -115,6 +115,15 @@ int mass_solve(pfc_handle *h, const double *b, double *x, double *r, double *p, 
 }
 } // namespace
 
+// host-only view for the CPU tests (tests/test_reduced_cpu.py): out3 = {diag(S~), min, max of the Jacobi-scaled symbol}
+extern "C" int pfc_reduced_symbol(double hx, double hy, double dt_theta, double *out3)
+{
+  if (!out3 || !(hx > 0) || !(hy > 0))
+    return PFC_ERR_BAD_ARGUMENT;
+  stilde_symbol(hx, hy, dt_theta, out3[0], out3[1], out3[2]);
+  return PFC_OK;
+}
+
 // end of pfc_setup on the Q1 lattice path: work fields, the constant Jacobi scaling and the Chebyshev coefficients
 int reduced_setup(pfc_handle *h)
 {
