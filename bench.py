@@ -111,8 +111,34 @@ class ClockSampler:
         self.index, self.samples, self._stop = index, [], threading.Event()
         self._t = threading.Thread(target=self._run, daemon=True)
 
+    def _nvml_open(self):
+        """NVML handle of the GPU (a sample costs microseconds: a 0.2 s timed region still gets several), or None"""
+        try:
+            import pynvml as N
+            N.nvmlInit()
+            h = N.nvmlDeviceGetHandleByIndex(self.index)
+            reasons = getattr(N, "nvmlDeviceGetCurrentClocksEventReasons", None) or N.nvmlDeviceGetCurrentClocksThrottleReasons
+            N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM), reasons(h)  # fail here, not in the loop
+            return N, h, reasons
+        except Exception:
+            return None
+
     def _run(self):
+        nv = self._nvml_open()
         while not self._stop.is_set():
+            try:
+                if nv is not None:
+                    N, h, reasons = nv
+                    r = int(reasons(h))
+                    act = lambda bit: "Active" if r & bit else "Not Active"  # noqa: E731
+                    # bits of nvml.h: SwPowerCap 0x4, HwSlowdown 0x8, SwThermalSlowdown 0x20, HwThermalSlowdown 0x40
+                    self.samples.append([str(N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)),
+                                         str(N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)),
+                                         act(0x8), act(0x40), act(0x20), act(0x4)])
+                    self._stop.wait(0.02)
+                    continue
+            except Exception:
+                nv = None  # fall back to nvidia-smi for the rest of the run
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                       "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
