@@ -96,3 +96,50 @@ def test_symbol_matches_assembled_schur_stand_in(built, oracle_mod, n_refines, t
 def test_symbol_rejects_bad_arguments(built):
     with pytest.raises(ValueError):
         built.reduced_symbol(0.0, 1.0, 0.1)
+
+
+def _serial_class_solve(B, C, D, K, M, F, G, H):
+    """solve_and_update of the reference's serial class, restated line by line with scipy
+    (phase_field_crystal_system.cpp:319-369): M_chi_inv / M_phi_inv = CG with Jacobi and ReductionControl(2000, 1e-18, 1e-10)
+    (:321-339), psi_matrix = B + (D M_phi_inv L_chi - C) M_chi_inv L_psi (:347), psi_rhs (:353-355), GMRES with
+    SolverControl(500) (default tolerance 1e-10) and PreconditionIdentity (:357-359), back substitution (:361-365).
+    L_psi = L_chi = K and M_chi = M_phi = M on this mesh.  TEST INFRASTRUCTURE."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from study_reduced import Op, gmres_right_x
+    jac = spl.LinearOperator(M.shape, matvec=lambda v, d=M.diagonal(): v / d)
+
+    def m_inv(b):
+        if not np.any(b):
+            return np.zeros_like(b)
+        x, info = spl.cg(M, b, rtol=1e-10, atol=1e-18, maxiter=2000, M=jac)
+        assert info == 0
+        return x
+    psi_matrix = Op(lambda v: B @ v + D @ m_inv(K @ m_inv(K @ v)) - C @ m_inv(K @ v))
+    psi_rhs = F - C @ m_inv(G) + D @ m_inv(K @ m_inv(G) - H)
+    dpsi, its, res = gmres_right_x(psi_matrix, psi_rhs, lambda v: v, tol=1e-10, restart=28, maxit=500)
+    dchi = m_inv(G - K @ dpsi)
+    dphi = m_inv(H - K @ dchi)
+    return np.concatenate([dpsi, dchi, dphi]), its, res
+
+
+def test_reduced_update_equals_the_serial_class_solve(oracle_mod):
+    """The update of the reduced formulation (dpsi = M^2 y, no mass solve inside the operator) against the serial class's own
+    Schur solve with its CG mass inverses, on the same Newton system (first iteration of a step: G, H != 0)."""
+    O = oracle_mod
+    p1, p2 = (-6 * A, -5 * A), (6 * A, 5 * A)
+    om, free, blk, (F, G, H) = _blocks(O, 4, 1.0, p1, p2, perturb=False)
+    B, C, D, K, M = blk(0, 0), blk(0, 1), blk(0, 2), blk(1, 0), blk(1, 1)
+    assert np.linalg.norm(G) > 1e-3  # chi = phi = 0 in the initial condition: the auxiliary rows are violated
+    ref, its, res = _serial_class_solve(B, C, D, K, M, F, G, H)
+    assert res <= 1e-10 and its < 500
+    Mi = spl.factorized(M.tocsc())
+    u = Mi(G)
+    w = Mi(K @ u - H)
+    T = (B @ M @ M + D @ K @ K - C @ K @ M).tocsc()
+    y = spl.spsolve(T, F - C @ u + D @ w)
+    mine = np.concatenate([M @ (M @ y), u - K @ (M @ y), K @ (K @ y) - w])
+    n = len(free)
+    assert np.linalg.norm(mine[:n] - ref[:n]) <= 1e-7 * np.linalg.norm(ref[:n])
+    assert np.linalg.norm(mine - ref) <= 1e-7 * np.linalg.norm(ref)
