@@ -24,7 +24,9 @@ struct Options
   double dt, theta, eps, newton_tol;
   unsigned int newton_max_iters;
   int operator_kind  = PFC_OPERATOR_MATRIX_FREE;  // lattice kernels on make_grid's meshes; 0 = assembled, bit-exact pattern
-  int preconditioner = PFC_PRECOND_BLOCK_SCHUR;   // PFC_PRECOND_NONE = solve_and_update_no_precondition as upstream
+  int preconditioner = PFC_PRECOND_BLOCK_SCHUR;   // PFC_PRECOND_NONE = solve_and_update_no_precondition as upstream;
+                                                  // PFC_PRECOND_SCHUR_REDUCED = the serial class's psi-only Schur solve
+                                                  // (fastest on FE_Q(1) + matrix-free; elsewhere it acts as BLOCK_SCHUR)
   int gpus_per_node  = 8;
 };
 

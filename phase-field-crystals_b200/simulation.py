@@ -29,7 +29,8 @@ class HexagonalLattice:
 class PhaseFieldCrystalSystemMPI:
     """mpi.hpp:30-51.  Extra keyword arguments (not in the reference): rank / n_ranks / nccl_id for one process per GPU,
     `log` (pcout), and Solver options (operator_kind, preconditioner, device ...); the default is the matrix-free lattice
-    path with the block-Schur preconditioner, `operator_kind=0, preconditioner=0` is the reference's algorithm."""
+    path with the block-Schur preconditioner, `operator_kind=0, preconditioner=0` is the reference's algorithm,
+    `preconditioner=2` the psi-only reduced solve (Q1; include/pfc_b200.h PFC_PRECOND_SCHUR_REDUCED)."""
 
     def __init__(self, degree, data_folder, configuration_filename, rhs_filename, output_interval, eps, dt, n_timesteps,
                  theta, simulation_tol, simulation_max_iters, n_refines, lower_left, upper_right, initial_condition, *,
